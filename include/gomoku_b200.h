@@ -1,0 +1,198 @@
+/*
+ * gomoku_b200.h -- C ABI of the B200-native batched self-play engine (libgomoku_b200.so).
+ *
+ * The reference (gitMasterLiujiahui/AlphaZero-Gomoku) is pure Python and has no FFI layer; its
+ * boundary for the MCTS hot path is the Python class surface AlphaZeroGomokuAI.get_move /
+ * GomokuModel.predict.  The drop-in Python modules in alphazero-gomoku_b200/ keep that surface and
+ * call the entry points below through ctypes.  Each entry point cites the reference code it
+ * replaces (file:line, relative to the reference root).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative gz_status otherwise; gz_last_error() gives
+ *     the message of the last failure on the calling thread.  No exception crosses the ABI.
+ *   - pointers named d_* are DEVICE pointers owned by the caller (e.g. torch tensors); pointers
+ *     named h_* are HOST pointers.  `stream` is a cudaStream_t passed as void* (NULL = default).
+ *   - one handle per GPU; a handle is not thread-safe.
+ *   - cells are raster order, index = row*15 + col; 0 empty, 1 black, 2 white
+ *     (gomoku_board.py:26-29).  Bitsets over cells are 8 x uint32, bit i of the 225-bit raster set
+ *     at word i/32, bit i%32.
+ *   - there is no CPU fallback: every compute call fails with GZ_ERR_CUDA if no device is present.
+ */
+#ifndef GOMOKU_B200_H
+#define GOMOKU_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gz_engine *gz_handle;
+
+typedef enum {
+    GZ_OK = 0,
+    GZ_ERR_ARG = -1,     /* bad argument (null pointer, size out of range, weights not set) */
+    GZ_ERR_CUDA = -2,    /* CUDA runtime / driver error, including "no device" */
+    GZ_ERR_ALLOC = -3,   /* out of device memory */
+    GZ_ERR_STATE = -4    /* call out of order (e.g. gz_get_tree before gz_search) */
+} gz_status;
+
+/* Board state in HBM.  Replaces GomokuBoard's int64[15,15] array + history list
+ * (gomoku_board.py:40-53): two 256-bit bitboards with a 16-column pitch, bit 16*row+col; column 15
+ * and row 15 are always zero so that shifts by 1/15/16/17 never wrap into a real cell. 80 bytes. */
+typedef struct {
+    uint32_t stones[2][8]; /* [0] black, [1] white */
+    uint16_t move_count;   /* len(move_history) */
+    uint8_t to_move;       /* current_player: 1 black, 2 white */
+    uint8_t status;        /* 0 live, 1 black won, 2 white won, 3 draw (game_over, winner) */
+    uint32_t reserved[3];
+} gz_board;
+
+typedef struct {
+    int32_t device;          /* CUDA ordinal */
+    int32_t max_games;       /* capacity G of every batched call */
+    int32_t max_simulations; /* capacity S; a tree holds at most S+1 nodes (one node per simulation,
+                                ai_agent.py:206-222) */
+    int32_t precision;       /* 0 = fp32 FFMA networks (parity mode, 1e-4),
+                                1 = bf16 tcgen05 networks (throughput mode, 2e-2) */
+    int32_t store_priors;    /* keep MCTSNode.prior_prob per node (ai_agent.py:523,564-582) */
+} gz_config;
+
+/* Mirrors AlphaZeroGomokuAI.params + ctor arguments (ai_agent.py:29-31,65-92) and
+ * BGPlannerAI.params (bg_planner.py:215-219); re-read at every call because callers mutate
+ * ai.params after construction (training.py:240,246). */
+typedef struct {
+    int32_t num_simulations;
+    int32_t planner_steps;
+    int32_t planner_k;       /* 8 / 12 / 16 */
+    int32_t deterministic;   /* 1: random.choice -> seq[0], random.random -> 1.0 */
+    double c_puct;
+    double beta;
+    double planner_alpha;    /* 0.5 / 0.65 / 0.75 */
+    double planner_explore;  /* 0.2 / 0.1 / 0.05 */
+    uint64_t seed;           /* Philox key */
+    uint32_t game_base;      /* global id of game 0 of this call (multi-GPU sharding keeps streams
+                                independent of the GPU count) */
+    int32_t eval_nodes;      /* 1: run the policy-value net for every created non-terminal node, as
+                                the reference does (ai_agent.py:522-523); 0 skips it (diagnostic) */
+} gz_search_params;
+
+typedef struct {
+    int64_t simulations;     /* _mcts_simulation calls executed */
+    int64_t nodes_created;
+    int64_t pv_evals;        /* policy-value forwards (non-terminal nodes created, roots included) */
+    int64_t planner_steps;   /* BGPlannerAI.get_move calls executed inside rollouts */
+    int64_t rollout_steps;   /* _select_offensive_move calls executed */
+    int64_t terminal_leaves; /* simulations whose leaf was already game_over */
+    int64_t kernel_launches; /* engine kernels launched since gz_create / last reset */
+} gz_counters;
+
+/* ---- life cycle --------------------------------------------------------------------------- */
+int gz_create(const gz_config *cfg, gz_handle *out);
+int gz_destroy(gz_handle h);
+const char *gz_last_error(void);
+int gz_version(void);
+
+/* ---- weights and tables ------------------------------------------------------------------- */
+/* GomokuModel.load_model / `ai.model = ...` (neural_network.py:310-333, training.py:247-248):
+ * h_flat is AlphaZeroGomokuNet.state_dict() flattened in state-dict order, fp32, without the
+ * num_batches_tracked counters (gz_pv_param_count() floats).  BatchNorm (eval mode, eps 1e-5,
+ * neural_network.py:142,87-88) is folded into the convolutions here. */
+int gz_set_pv_weights(gz_handle h, const float *h_flat, int64_t n);
+/* BGPlannerAI's GraphNet and OpponentDQN (bg_planner.py:210-211), same flattening. */
+int gz_set_planner_weights(gz_handle h, const float *h_graphnet, int64_t n_graphnet,
+                           const float *h_dqn, int64_t n_dqn);
+/* Host-computed np.log(n) and np.tanh(i*50/10000.0) tables, so that the float64 selection score
+ * (ai_agent.py:532-562) is bit-identical to numpy's on the calling host.  Optional: without them the
+ * device's log()/tanh() are used. */
+int gz_set_tables(gz_handle h, const double *h_log, int32_t n_log, const double *h_tanh,
+                  int32_t n_tanh);
+int64_t gz_pv_param_count(void);
+int64_t gz_graphnet_param_count(void);
+int64_t gz_dqn_param_count(void);
+
+/* ---- boards (gomoku_board.py) -------------------------------------------------------------- */
+/* GomokuBoard -> bitboards.  d_cells u8[G,225]; d_to_move u8[G]; d_move_count u16[G].  status is
+ * derived: a five (or more) of either colour, else draw when move_count >= 200
+ * (gomoku_board.py:103-108). */
+int gz_boards_from_cells(gz_handle h, const uint8_t *d_cells, const uint8_t *d_to_move,
+                         const uint16_t *d_move_count, int32_t G, gz_board *d_boards, void *stream);
+/* Inverse, for inspection: u8[G,225]. */
+int gz_boards_to_cells(gz_handle h, const gz_board *d_boards, int32_t G, uint8_t *d_cells,
+                       void *stream);
+/* make_move (gomoku_board.py:84-113) for one move per board; d_moves i32[G] raster index;
+ * d_ok u8[G] receives make_move's return value. */
+int gz_make_moves(gz_handle h, gz_board *d_boards, const int32_t *d_moves, int32_t G, uint8_t *d_ok,
+                  void *stream);
+/* Per-board analysis, the parity surface of the board kernel.  Any output pointer may be NULL.
+ *   d_legal      u32[G,8]    get_valid_moves as a raster bitset       gomoku_board.py:201-213
+ *   d_win_cells  u32[G,2,8]  empty cells where a stone of colour p makes five    :139-165
+ *   d_three_cells u32[G,2,8] empty cells where a stone of p gives threat level >= 3   ai_agent.py:383-401
+ *   d_threat     i32[G,2]    _evaluate_threat_level for black, white  ai_agent.py:403-430
+ *   d_pattern    i64[G,2]    KnowledgeSearch._pattern_score           bg_planner.py:133-196 */
+int gz_board_ops(gz_handle h, const gz_board *d_boards, int32_t G, uint32_t *d_legal,
+                 uint32_t *d_win_cells, uint32_t *d_three_cells, int32_t *d_threat,
+                 int64_t *d_pattern, void *stream);
+
+/* ---- networks ------------------------------------------------------------------------------ */
+/* GomokuModel.predict batched (neural_network.py:214-252, forward :132-159): planes are generated
+ * from the bitboards in-kernel.  d_logits f32[G,225], d_probs f32[G,225] (softmax over all 225
+ * cells), d_value f32[G] (tanh).  Any output may be NULL. */
+int gz_pv_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_logits, float *d_probs,
+                  float *d_value, void *stream);
+/* GraphNet.forward + softmax and OpponentDQN.forward (bg_planner.py:50-56,74-78,243-250):
+ * d_gn_logits f32[G,225], d_gn_policy f32[G,225], d_dqn_q f32[G,225]. */
+int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_gn_logits,
+                            float *d_gn_policy, float *d_dqn_q, void *stream);
+
+/* ---- planner move (bg_planner.py:232-269) --------------------------------------------------- */
+/* One BGPlannerAI.get_move per board.  d_ai_player u8[G] is the planner's fixed colour
+ * (ai_agent.py:60).  Outputs (any may be NULL):
+ *   d_scores2  i64[G,225]  2*score_move for every empty cell (exact integers; occupied = INT64_MIN)
+ *   d_topk     i32[G,16]   stable descending top-k, -1 padded              bg_planner.py:108-114
+ *   d_composed f64[G,16]   alpha*policy - (1-alpha)*q per candidate        :256-264
+ *   d_move     i32[G]      the move returned (-1 if the board has no empty cell)
+ * `step` is the rollout step index used to key the explore roll. */
+int gz_planner_move(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player, int32_t G,
+                    const gz_search_params *p, int32_t sim, int32_t step, int64_t *d_scores2,
+                    int32_t *d_topk, double *d_composed, int32_t *d_move, void *stream);
+
+/* ---- rollout (ai_agent.py:251-430) ----------------------------------------------------------- */
+/* One _select_offensive_move per board: d_move i32[G]; d_cand u32[G,8] = the candidate list handed
+ * to random.choice (all zero when tier 1 returned a winning move). */
+int gz_rollout_policy(gz_handle h, const gz_board *d_boards, int32_t G, const gz_search_params *p,
+                      int32_t sim, int32_t step, int32_t *d_move, uint32_t *d_cand, void *stream);
+/* One _simulate per board: up to planner_steps planner moves, then the offensive-random tail, at
+ * most 100 steps in total.  d_value f64[G] in {1,-1,0.1,0}; d_steps i32[G]; d_final the final
+ * rollout boards (may be NULL). */
+int gz_rollout(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player, int32_t G,
+               const gz_search_params *p, int32_t sim, double *d_value, int32_t *d_steps,
+               gz_board *d_final, void *stream);
+
+/* ---- search (ai_agent.py:168-249,441-454,532-562) --------------------------------------------- */
+/* One _mcts_search per board, all G trees advanced in lock-step, one simulation in flight per tree.
+ *   d_child_visits i32[G,225], d_child_value f64[G,225]: root children indexed by move (0 where the
+ *   root has no such child); d_best_move i32[G]: first root child with maximal visits
+ *   (ai_agent.py:199-201), -1 if the root has no child. */
+int gz_search(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player, int32_t G,
+              const gz_search_params *p, int32_t *d_child_visits, double *d_child_value,
+              int32_t *d_best_move, void *stream);
+/* Same through HOST buffers, the call behind AlphaZeroGomokuAI.get_move: copies the positions in,
+ * searches, copies the answers out, synchronises.  h_cells u8[G,225], h_to_move u8[G],
+ * h_move_count u16[G], h_ai_player u8[G]; outputs as gz_search (any may be NULL). */
+int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t *h_to_move,
+                   const uint16_t *h_move_count, const uint8_t *h_ai_player, int32_t G,
+                   const gz_search_params *p, int32_t *h_child_visits, double *h_child_value,
+                   int32_t *h_best_move);
+/* Whole tree of game g after gz_search, creation order (node 0 = root): host arrays of `cap`
+ * entries; *n_nodes receives the node count. */
+int gz_get_tree(gz_handle h, int32_t g, int32_t cap, int32_t *h_parent, int32_t *h_move,
+                int32_t *h_visits, double *h_value, int32_t *n_nodes);
+
+/* ---- counters ---------------------------------------------------------------------------------- */
+int gz_get_counters(gz_handle h, gz_counters *out);
+int gz_reset_counters(gz_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,210 @@
+"""ctypes binding of oracle/libgomoku_oracle.so.  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this
+module; the product package never does (a test greps for it).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class Board(C.Structure):
+    _fields_ = [("cells", C.c_int8 * 225), ("to_move", C.c_int32), ("move_count", C.c_int32),
+                ("game_over", C.c_int32), ("winner", C.c_int32)]
+
+
+class Rng(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("seed_lo", C.c_uint32), ("seed_hi", C.c_uint32),
+                ("game", C.c_uint32), ("sim", C.c_uint32)]
+
+
+class Weights(C.Structure):
+    _fields_ = [("pv", C.c_void_p), ("graphnet", C.c_void_p), ("dqn", C.c_void_p)]
+
+
+class Params(C.Structure):
+    _fields_ = [("num_simulations", C.c_int32), ("c_puct", C.c_double), ("beta", C.c_double),
+                ("planner_steps", C.c_int32), ("planner_k", C.c_int32), ("planner_alpha", C.c_double),
+                ("planner_explore", C.c_double), ("ai_player", C.c_int32), ("eval_nodes", C.c_int32),
+                ("log_table", C.c_void_p), ("n_log", C.c_int32),
+                ("tanh_table", C.c_void_p), ("n_tanh", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("best_move", C.c_int32), ("n_pv_evals", C.c_int64),
+                ("n_planner_steps", C.c_int64), ("n_rollout_steps", C.c_int64),
+                ("n_terminal_leaves", C.c_int64)]
+
+
+PLANNER_PRESETS = {"easy": (8, 0.5, 0.2), "medium": (12, 0.65, 0.1), "hard": (16, 0.75, 0.05)}
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libgomoku_oracle.so")
+    src = [os.path.join(_HERE, f) for f in ("gomoku_oracle.c", "gomoku_oracle.h")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "libgomoku_oracle.so"],
+                              stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build())
+        L.gzo_pattern_score.restype = C.c_int64
+        L.gzo_simulate.restype = C.c_double
+        for f in ("gzo_pv_param_count", "gzo_graphnet_param_count", "gzo_dqn_param_count"):
+            getattr(L, f).restype = C.c_int64
+        _LIB = L
+    return _LIB
+
+
+def board_from_moves(moves):
+    L = lib()
+    b = Board()
+    L.gzo_board_init(C.byref(b))
+    for m in moves:
+        if m < 0:
+            break
+        assert L.gzo_make_move(C.byref(b), int(m) // 15, int(m) % 15) == 1
+    return b
+
+
+def board_from_cells(cells, to_move, move_count):
+    b = Board()
+    arr = np.ascontiguousarray(cells, dtype=np.uint8)
+    lib().gzo_board_from_cells(C.byref(b), arr.ctypes.data_as(C.c_void_p), int(to_move), int(move_count))
+    return b
+
+
+def cells_of(b):
+    return np.frombuffer(b.cells, dtype=np.int8).astype(np.uint8).copy()
+
+
+def flatten_state_dict(sd):
+    """state dict (name -> ndarray) -> one float32 vector in state-dict order, BN counters dropped."""
+    parts = [np.asarray(v, dtype=np.float32).reshape(-1) for k, v in sd.items()
+             if not k.endswith("num_batches_tracked")]
+    return np.ascontiguousarray(np.concatenate(parts))
+
+
+def log_table(n):
+    t = np.zeros(n, dtype=np.float64)
+    t[1:] = [float(np.log(i)) for i in range(1, n)]
+    return t
+
+
+def tanh_table(n=4096):
+    return np.array([float(np.tanh((i * 50.0) / 10000.0)) for i in range(n)], dtype=np.float64)
+
+
+class Oracle:
+    """Holds the flattened weights and tables and exposes the oracle's entry points."""
+
+    def __init__(self, pv=None, graphnet=None, dqn=None, use_tables=True):
+        self.L = lib()
+        self._keep = []
+        self.w = Weights()
+        for name, sd, cnt in (("pv", pv, self.L.gzo_pv_param_count()),
+                              ("graphnet", graphnet, self.L.gzo_graphnet_param_count()),
+                              ("dqn", dqn, self.L.gzo_dqn_param_count())):
+            if sd is not None:
+                flat = flatten_state_dict(sd)
+                assert flat.size == cnt, (name, flat.size, cnt)
+                self._keep.append(flat)
+                setattr(self.w, name, flat.ctypes.data)
+        self.logt = log_table(1024) if use_tables else None
+        self.tanht = tanh_table() if use_tables else None
+
+    def params(self, sims, c_puct, beta, planner_steps, ai_player, difficulty="hard", eval_nodes=0):
+        k, a, e = PLANNER_PRESETS.get(difficulty, PLANNER_PRESETS["medium"])
+        p = Params(int(sims), float(c_puct), float(beta), int(planner_steps), k, a, e, int(ai_player),
+                   int(eval_nodes), None, 0, None, 0)
+        if self.logt is not None:
+            p.log_table, p.n_log = self.logt.ctypes.data, self.logt.size
+            p.tanh_table, p.n_tanh = self.tanht.ctypes.data, self.tanht.size
+        return p
+
+    # ---- rules
+    def threat(self, b, player):
+        return self.L.gzo_threat_level(C.byref(b), player)
+
+    def pattern(self, b, player):
+        return int(self.L.gzo_pattern_score(C.byref(b), player))
+
+    def legal(self, b):
+        m = np.zeros(225, np.uint8)
+        self.L.gzo_legal_mask(C.byref(b), m.ctypes.data_as(C.c_void_p))
+        return m
+
+    # ---- rollout
+    def select_move(self, b, literal=False, rng=None, step=0):
+        cand = np.zeros(225, np.uint8)
+        fc = C.c_int(0)
+        f = self.L.gzo_select_offensive_move_literal if literal else self.L.gzo_select_offensive_move
+        mv = f(C.byref(b), C.byref(rng) if rng is not None else None, step,
+               cand.ctypes.data_as(C.c_void_p), C.byref(fc))
+        return mv, cand, fc.value
+
+    def simulate(self, b, p, rng=None):
+        fb = Board()
+        st = Stats()
+        v = self.L.gzo_simulate(C.byref(b), C.byref(p), C.byref(self.w),
+                                C.byref(rng) if rng is not None else None, C.byref(fb), C.byref(st))
+        return v, fb, st
+
+    # ---- planner
+    def planner_scores(self, b, ai_player):
+        s = np.zeros(225, np.float64)
+        self.L.gzo_planner_scores(C.byref(b), ai_player, s.ctypes.data_as(C.c_void_p))
+        return s
+
+    def planner_move(self, b, p, rng=None, step=0):
+        top = np.full(32, -1, np.int32)
+        comp = np.full(32, np.nan, np.float64)
+        mv = self.L.gzo_planner_move(C.byref(b), C.byref(p), C.byref(self.w),
+                                     C.byref(rng) if rng is not None else None, step,
+                                     top.ctypes.data_as(C.c_void_p), comp.ctypes.data_as(C.c_void_p))
+        return mv, top, comp
+
+    # ---- nets
+    def pv_forward(self, cells):
+        cells = np.ascontiguousarray(cells, np.uint8)
+        lg = np.zeros(225, np.float32); pr = np.zeros(225, np.float32); v = C.c_float(0)
+        self.L.gzo_pv_forward(C.c_void_p(self.w.pv), cells.ctypes.data_as(C.c_void_p),
+                              lg.ctypes.data_as(C.c_void_p), pr.ctypes.data_as(C.c_void_p), C.byref(v))
+        return lg, pr, v.value
+
+    def graphnet_forward(self, cells):
+        cells = np.ascontiguousarray(cells, np.uint8)
+        lg = np.zeros(225, np.float32)
+        self.L.gzo_graphnet_forward(C.c_void_p(self.w.graphnet), cells.ctypes.data_as(C.c_void_p),
+                                    lg.ctypes.data_as(C.c_void_p))
+        return lg
+
+    def dqn_forward(self, cells):
+        cells = np.ascontiguousarray(cells, np.uint8)
+        q = np.zeros(225, np.float32)
+        self.L.gzo_dqn_forward(C.c_void_p(self.w.dqn), cells.ctypes.data_as(C.c_void_p),
+                               q.ctypes.data_as(C.c_void_p))
+        return q
+
+    # ---- search
+    def search(self, b, p, seed=0, game=0):
+        n = p.num_simulations + 2
+        parent = np.full(n, -1, np.int32); move = np.full(n, -1, np.int32)
+        visits = np.zeros(n, np.int32); value = np.zeros(n, np.float64)
+        st = Stats()
+        self.L.gzo_search(C.byref(b), C.byref(p), C.byref(self.w), C.c_uint32(seed & 0xFFFFFFFF),
+                          C.c_uint32((seed >> 32) & 0xFFFFFFFF), C.c_uint32(game),
+                          parent.ctypes.data_as(C.c_void_p), move.ctypes.data_as(C.c_void_p),
+                          visits.ctypes.data_as(C.c_void_p), value.ctypes.data_as(C.c_void_p), n,
+                          C.byref(st))
+        k = st.n_nodes
+        return dict(parent=parent[:k], move=move[:k], visits=visits[:k], value=value[:k], stats=st)

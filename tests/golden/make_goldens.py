@@ -1,0 +1,631 @@
+#!/usr/bin/env python
+"""Generate the golden fixtures under tests/golden/ by running the UNMODIFIED reference.
+
+Runs only in the build container: it imports /root/reference (read-only) from a scratch cwd with no
+./models directory (neural_network.py:197-212 would silently load checkpoints from there), applies
+the deterministic-mode patches of SURVEY.md A.7 where a part says so, and writes small .npz files
+that travel with the repo.  Nothing under tests/, bench.py or smoke() reads /root/reference at run
+time; they read these fixtures.
+
+    python tests/golden/make_goldens.py --parts all --jobs 8
+
+Parts (each -> tests/golden/<part>.npz):
+  boards    rules + masks + threat levels + pattern scores            gomoku_board.py, ai_agent.py:403-430, bg_planner.py:133-196
+  tiers     candidate set handed to random.choice by the rollout policy   ai_agent.py:306-361
+  rollout   DET-A playouts (planner_steps=0): value, steps, final board   ai_agent.py:251-304
+  mcts      DET-A searches: the whole tree (parent, move, visits, value)  ai_agent.py:168-249,441-454,532-562
+  planner   knowledge-search scores, stable top-k, blended pick (DET-B)  bg_planner.py:90-131,232-269
+  nets      logits / value / softmax of the three networks (fp32, 1 thread)   neural_network.py:132-159,214-252
+  mctsb     DET-B playouts and searches (planner_steps>0)
+  stoch     outcome frequencies of real-RNG playouts (Mersenne Twister)
+"""
+import argparse
+import os
+import sys
+import tempfile
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, "/root/reference")
+_SCRATCH = tempfile.mkdtemp(prefix="gz_golden_")
+os.chdir(_SCRATCH)
+
+import random  # noqa: E402
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+torch.set_num_threads(1)
+
+import gomoku_board  # noqa: E402
+import ai_agent  # noqa: E402
+import bg_planner  # noqa: E402
+import neural_network  # noqa: E402
+from gomoku_board import GomokuBoard  # noqa: E402
+from weights import make_state_dict  # noqa: E402
+
+WEIGHT_SEED = 1234
+_ORIG_CHOICE = random.choice
+_ORIG_RANDOM = random.random
+
+
+# ----------------------------------------------------------------------------- helpers
+def det_patch():
+    random.choice = lambda s: s[0]
+    random.random = lambda: 1.0
+
+
+def det_unpatch():
+    random.choice = _ORIG_CHOICE
+    random.random = _ORIG_RANDOM
+
+
+def board_from_moves(moves):
+    b = GomokuBoard()
+    for m in moves:
+        ok = b.make_move(int(m) // 15, int(m) % 15)
+        assert ok, "illegal move in a generated sequence"
+    return b
+
+
+def cells_of(b):
+    return b.board.astype(np.uint8).reshape(225)
+
+
+def load_weights(module, kind, gain=None):
+    sd = make_state_dict(kind, WEIGHT_SEED, gain)
+    module.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}, strict=True)
+    module.eval()
+
+
+def make_ai(player, difficulty="hard", planner_steps=0, beta=0.2, sims=None, c_puct=None):
+    ai = ai_agent.AlphaZeroGomokuAI(player, difficulty, device="cpu", beta=beta,
+                                    planner_steps=planner_steps, time_limit=float("inf"))
+    load_weights(ai.model.model, "pv")
+    load_weights(ai.bg_planner.graph_net, "graphnet")
+    load_weights(ai.bg_planner.opp_dqn, "dqn")
+    ai.params = dict(ai.params)
+    if sims is not None:
+        ai.params["num_simulations"] = int(sims)
+    if c_puct is not None:
+        ai.params["c_puct"] = float(c_puct)
+    return ai
+
+
+# ----------------------------------------------------------------------------- positions
+def _interleave(black, white):
+    assert len(black) in (len(white), len(white) + 1)
+    out = []
+    for i in range(len(black)):
+        out.append(black[i][0] * 15 + black[i][1])
+        if i < len(white):
+            out.append(white[i][0] * 15 + white[i][1])
+    return out
+
+
+def tactical_positions():
+    """Hand-built boards: win-in-1, open three/four, edges, corners, overline, both sides armed."""
+    P = []
+    # black open four in the middle, white to move
+    P.append(_interleave([(7, 3), (7, 4), (7, 5), (7, 6)], [(0, 0), (0, 2), (0, 4), (0, 6)]))
+    # same, black to move (win-in-1 at two cells)
+    P.append(_interleave([(7, 3), (7, 4), (7, 5), (7, 6)], [(0, 0), (0, 2), (0, 4)])[:7] + [0 * 15 + 8])
+    # white three in a column touching the top edge, black scattered
+    P.append(_interleave([(14, 0), (14, 2), (14, 4), (12, 7)], [(0, 5), (1, 5), (2, 5)]))
+    # black run of four into the top-left corner along the diagonal
+    P.append(_interleave([(0, 0), (1, 1), (2, 2), (3, 3)], [(0, 14), (2, 14), (4, 14), (6, 14)]))
+    # anti-diagonal run of four ending at the bottom-left corner, white to move
+    P.append(_interleave([(14, 0), (13, 1), (12, 2), (11, 3)], [(0, 1), (0, 3), (0, 5), (0, 7)]))
+    # overline shape XXX_XX for black (filling the gap makes six), black to move
+    P.append(_interleave([(5, 2), (5, 3), (5, 4), (5, 6), (5, 7)], [(9, 0), (9, 2), (9, 4), (9, 6), (9, 8)]))
+    # broken three XX.X and X.XX for white, row 14 (bottom edge) and col 14 (right edge)
+    P.append(_interleave([(7, 7), (0, 0), (0, 2), (2, 0), (2, 2), (4, 0)],
+                         [(14, 3), (14, 4), (14, 6), (3, 14), (5, 14), (6, 14)]))
+    # both players have a four: the mover wins first
+    P.append(_interleave([(3, 3), (3, 4), (3, 5), (3, 6)], [(10, 3), (10, 4), (10, 5), (10, 6)]))
+    P.append(_interleave([(3, 3), (3, 4), (3, 5), (3, 6), (12, 12)], [(10, 3), (10, 4), (10, 5), (10, 6)]))
+    # right-edge horizontal four for black ending at col 14 (one open end only)
+    P.append(_interleave([(6, 11), (6, 12), (6, 13), (6, 14)], [(8, 0), (8, 2), (8, 4), (8, 6)]))
+    # live two / live three mix around the centre
+    P.append(_interleave([(7, 7), (7, 8), (9, 9), (10, 10)], [(6, 6), (5, 5), (8, 3), (8, 4)]))
+    # vertical white open three, black has a diagonal broken three
+    P.append(_interleave([(4, 4), (5, 5), (7, 7), (11, 2)], [(6, 10), (7, 10), (8, 10)]))
+    # finished games: black five, white five, black six (overline) -> game_over boards
+    P.append(_interleave([(7, 3), (7, 4), (7, 5), (7, 6), (7, 7)], [(0, 0), (0, 2), (0, 4), (0, 6)]))
+    P.append(_interleave([(0, 0), (0, 2), (0, 4), (0, 6), (2, 0)], [(10, 14), (11, 13), (12, 12), (13, 11), (14, 10)]))
+    P.append(_interleave([(5, 2), (5, 3), (5, 4), (5, 6), (5, 7), (5, 5)], [(9, 0), (9, 2), (9, 4), (9, 6), (9, 8)]))
+    return P
+
+
+def dense_pattern_moves(rng, n_stones):
+    """A legal alternating move sequence of n_stones on the colouring ((r+2c) mod 4 < 2 -> black),
+    which has no run longer than two in any direction, in a random order.  Used for late-game
+    boards (draw at 200 stones, gomoku_board.py:106)."""
+    blk = [(r, c) for r in range(15) for c in range(15) if (r + 2 * c) % 4 < 2]
+    wht = [(r, c) for r in range(15) for c in range(15) if (r + 2 * c) % 4 >= 2]
+    rng.shuffle(blk)
+    rng.shuffle(wht)
+    nb, nw = (n_stones + 1) // 2, n_stones // 2
+    return _interleave(blk[:nb], wht[:nw])
+
+
+def random_position(rng, plies, style):
+    b = GomokuBoard()
+    seq = []
+    while b.get_move_count() < plies:
+        vm = b.get_valid_moves()
+        for _try in range(50):
+            if style == "cluster" and b.get_move_count() > 0:
+                occ = np.argwhere(b.board != 0)
+                near = [m for m in vm if np.min(np.max(np.abs(occ - np.array(m)), axis=1)) <= 2]
+                pool = near or vm
+            elif style == "centre":
+                pool = [m for m in vm if abs(m[0] - 7) + abs(m[1] - 7) <= 6] or vm
+            else:
+                pool = vm
+            mv = pool[int(rng.integers(len(pool)))]
+            t = b.copy_board()
+            t.make_move(*mv)
+            if not t.game_over:
+                break
+        else:
+            break
+        b.make_move(*mv)
+        seq.append(mv[0] * 15 + mv[1])
+    return seq
+
+
+def policy_position(seed, plies):
+    """Positions reached by the reference's own rollout policy with its real RNG (runs of 3-4 appear)."""
+    det_unpatch()
+    random.seed(seed)
+    ai = ai_agent.AlphaZeroGomokuAI(1, "easy", device="cpu", planner_steps=0)
+    b = GomokuBoard()
+    b.make_move(7, 7)
+    seq = [7 * 15 + 7]
+    while b.get_move_count() < plies:
+        mv = ai._select_offensive_move(b, b.get_valid_moves())
+        t = b.copy_board()
+        t.make_move(*mv)
+        if t.game_over:
+            break
+        b.make_move(*mv)
+        seq.append(mv[0] * 15 + mv[1])
+    return seq
+
+
+def build_position_set():
+    """The shared position list (move sequences).  Deterministic: PCG64 + Mersenne seeds."""
+    rng = np.random.default_rng(20261104)
+    pos = []
+    tags = []
+    for p in tactical_positions():
+        pos.append(p); tags.append("tactical")
+    for plies in (6, 7, 12, 13, 24, 25, 48, 49, 96, 97, 150, 151):
+        for style in ("uniform", "cluster", "centre"):
+            for _rep in range(3):
+                pos.append(random_position(rng, plies, style)); tags.append(style)
+    for n in (120, 150, 170, 171, 180, 190, 195, 196, 197, 198, 199):
+        for _rep in range(3):
+            pos.append(dense_pattern_moves(rng, n)); tags.append("dense")
+    return pos, tags
+
+
+def pad_moves(seqs, width=200):
+    out = np.full((len(seqs), width), -1, dtype=np.int16)
+    for i, s in enumerate(seqs):
+        out[i, :len(s)] = s
+    return out
+
+
+# ----------------------------------------------------------------------------- part: positions
+def part_positions(pool, outdir):
+    pos, tags = build_position_set()
+    specs = [(1000 + i, pl) for i, pl in enumerate((10, 14, 18, 22, 26, 30, 34, 38, 44, 50, 60, 70,
+                                                    11, 15, 19, 23, 27, 31, 35, 39, 45, 51, 61, 71))]
+    for seq in pool.starmap(policy_position, specs):
+        pos.append(seq); tags.append("policy")
+    np.savez_compressed(os.path.join(outdir, "positions.npz"), moves=pad_moves(pos),
+                        tags=np.array(tags))
+    print("positions:", len(pos))
+
+
+def load_positions(outdir):
+    z = np.load(os.path.join(outdir, "positions.npz"))
+    return [[int(m) for m in row if m >= 0] for row in z["moves"]], list(z["tags"])
+
+
+# ----------------------------------------------------------------------------- part: boards
+def _board_task(seq):
+    b = board_from_moves(seq)
+    ai = _board_task.ai
+    ks = _board_task.ks
+    rec = {}
+    rec["cells"] = cells_of(b)
+    rec["to_move"] = b.current_player
+    rec["move_count"] = b.get_move_count()
+    rec["game_over"] = int(b.game_over)
+    rec["winner"] = 0 if b.winner is None else int(b.winner)
+    legal = np.zeros(225, np.uint8)
+    for (r, c) in b.get_valid_moves():
+        legal[r * 15 + c] = 1
+    rec["legal"] = legal
+    rec["threat"] = np.array([ai._evaluate_threat_level(b, 1), ai._evaluate_threat_level(b, 2)], np.int32)
+    rec["pattern"] = np.array([ks._pattern_score(b, 1), ks._pattern_score(b, 2)], np.float64)
+    # win_cells[p]: empty cells where a stone of p ends the game with winner p (forced mover),
+    # three_cells[p]: empty cells where a stone of p gives threat level >= 3 for p
+    win = np.zeros((2, 225), np.uint8)
+    three = np.zeros((2, 225), np.uint8)
+    status_after = np.zeros((2, 225), np.uint8)   # 0 live, 1/2 winner, 3 draw, 255 illegal
+    status_after[:] = 255
+    if not b.game_over:
+        for p in (1, 2):
+            for (r, c) in b.get_valid_moves():
+                t = b.copy_board()
+                t.current_player = p
+                t.make_move(r, c)
+                if t.game_over and t.winner == p:
+                    win[p - 1, r * 15 + c] = 1
+                if ai._evaluate_threat_level(t, p) >= 3:
+                    three[p - 1, r * 15 + c] = 1
+                status_after[p - 1, r * 15 + c] = (0 if not t.game_over else (3 if t.winner is None else t.winner))
+    rec["win_cells"] = win
+    rec["three_cells"] = three
+    rec["status_after"] = status_after
+    return rec
+
+
+def _init_board_task():
+    _board_task.ai = ai_agent.AlphaZeroGomokuAI(1, "easy", device="cpu", planner_steps=0)
+    _board_task.ks = bg_planner.KnowledgeSearch(15)
+
+
+def part_boards(pool, outdir):
+    pos, _ = load_positions(outdir)
+    # also every prefix of a few sequences, so that make_move trajectories (win / draw detection at
+    # each ply) are covered, including the 200-stone draw
+    rng = np.random.default_rng(7)
+    extra = []
+    for n in (199, 198):
+        s = dense_pattern_moves(rng, n)
+        b = board_from_moves(s)
+        for mv in b.get_valid_moves()[:6]:
+            extra.append(s + [mv[0] * 15 + mv[1]])
+            if n == 198:
+                base = extra[-1]
+                b2 = board_from_moves(base)
+                for mv2 in ([] if b2.game_over else b2.get_valid_moves()[:3]):
+                    extra.append(base + [mv2[0] * 15 + mv2[1]])
+    allpos = pos + extra
+    recs = pool.map(_board_task, allpos, chunksize=4)
+    out = {k: np.stack([np.asarray(r[k]) for r in recs]) for k in recs[0]}
+    out["moves"] = pad_moves(allpos, 201)
+    np.savez_compressed(os.path.join(outdir, "boards.npz"), **out)
+    print("boards:", len(allpos))
+
+
+# ----------------------------------------------------------------------------- part: tiers
+def _tier_task(seq):
+    b = board_from_moves(seq)
+    if b.game_over:
+        return None
+    ai = _board_task.ai
+    seen = []
+
+    def rec_choice(s):
+        seen.append(list(s))
+        return s[0]
+    random.choice = rec_choice
+    mv = ai._select_offensive_move(b, b.get_valid_moves())
+    det_unpatch()
+    cand = np.zeros(225, np.uint8)
+    if seen:
+        for (r, c) in seen[0]:
+            cand[r * 15 + c] = 1
+    return dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(),
+                move=mv[0] * 15 + mv[1], from_choice=int(bool(seen)), cand=cand)
+
+
+def part_tiers(pool, outdir):
+    pos, _ = load_positions(outdir)
+    recs = [r for r in pool.map(_tier_task, pos, chunksize=2) if r is not None]
+    out = {k: np.stack([np.asarray(r[k]) for r in recs]) for k in recs[0]}
+    np.savez_compressed(os.path.join(outdir, "tiers.npz"), **out)
+    print("tiers:", len(recs))
+
+
+# ----------------------------------------------------------------------------- part: rollout (DET-A / DET-B)
+def _rollout_task(args):
+    seq, planner_steps, ai_player = args
+    b = board_from_moves(seq)
+    if b.game_over:
+        return None
+    det_patch()
+    ai = make_ai(ai_player, "hard", planner_steps=planner_steps)
+    final = {}
+    orig = ai._get_terminal_value
+
+    def spy(board):
+        final["cells"] = cells_of(board)
+        final["move_count"] = board.get_move_count()
+        final["game_over"] = int(board.game_over)
+        final["winner"] = 0 if board.winner is None else int(board.winner)
+        return orig(board)
+    ai._get_terminal_value = spy
+
+    class N:  # the only attributes _simulate reads (ai_agent.py:258-261)
+        board = b
+
+        @staticmethod
+        def is_terminal():
+            return b.game_over
+    v = ai._simulate(N)
+    det_unpatch()
+    return dict(start_cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(),
+                ai_player=ai_player, planner_steps=planner_steps, value=float(v),
+                final_cells=final["cells"], final_move_count=final["move_count"],
+                final_game_over=final["game_over"], final_winner=final["winner"],
+                steps=final["move_count"] - b.get_move_count())
+
+
+def part_rollout(pool, outdir):
+    pos, tags = load_positions(outdir)
+    live = [p for p in pos if not board_from_moves(p).game_over]
+    sel = live[::2]
+    tasks = [(p, 0, 1 + (i % 2)) for i, p in enumerate(sel)]
+    recs = [r for r in pool.map(_rollout_task, tasks, chunksize=1) if r is not None]
+    out = {k: np.stack([np.asarray(r[k]) for r in recs]) for k in recs[0]}
+    np.savez_compressed(os.path.join(outdir, "rollout.npz"), **out)
+    print("rollout:", len(recs))
+
+
+# ----------------------------------------------------------------------------- part: mcts (whole tree)
+def _mcts_task(args):
+    seq, ai_player, sims, c_puct, beta, planner_steps, difficulty = args
+    b = board_from_moves(seq)
+    det_patch()
+    ai = make_ai(ai_player, difficulty, planner_steps=planner_steps, beta=beta, sims=sims, c_puct=c_puct)
+    nodes = []
+    orig_init = ai_agent.MCTSNode.__init__
+
+    def spy_init(self, *a, **k):
+        nodes.append(self)
+        orig_init(self, *a, **k)
+    ai_agent.MCTSNode.__init__ = spy_init
+    t0 = time.time()
+    try:
+        best = ai._mcts_search(b, b.get_valid_moves())
+    finally:
+        ai_agent.MCTSNode.__init__ = orig_init
+        det_unpatch()
+    idx = {id(n): i for i, n in enumerate(nodes)}
+    n = len(nodes)
+    parent = np.array([-1 if x.parent is None else idx[id(x.parent)] for x in nodes], np.int32)
+    move = np.array([-1 if x.move is None else x.move[0] * 15 + x.move[1] for x in nodes], np.int32)
+    visits = np.array([x.visits for x in nodes], np.int32)
+    value = np.array([x.value for x in nodes], np.float64)
+    term = np.array([int(x.board.game_over) for x in nodes], np.uint8)
+    pat = np.array([ai.knowledge_search._pattern_score(x.board, ai.player) for x in nodes], np.float64)
+    return dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(),
+                ai_player=ai_player, sims=sims, c_puct=c_puct, beta=beta, planner_steps=planner_steps,
+                difficulty=difficulty, n_nodes=n, parent=parent, move=move, visits=visits, value=value,
+                terminal=term, pattern=pat, best_move=best[0] * 15 + best[1], seconds=time.time() - t0)
+
+
+def _save_trees(recs, path):
+    nmax = max(r["n_nodes"] for r in recs)
+    out = {}
+    for k in recs[0]:
+        v0 = recs[0][k]
+        if isinstance(v0, np.ndarray) and k in ("parent", "move", "visits", "value", "terminal", "pattern"):
+            fill = -1 if k in ("parent", "move") else 0
+            arr = np.full((len(recs), nmax), fill, dtype=v0.dtype)
+            for i, r in enumerate(recs):
+                arr[i, :r["n_nodes"]] = r[k]
+            out[k] = arr
+        else:
+            out[k] = np.stack([np.asarray(r[k]) for r in recs])
+    np.savez_compressed(path, **out)
+
+
+def part_mcts(pool, outdir):
+    pos, tags = load_positions(outdir)
+    live = [(p, t) for p, t in zip(pos, tags) if not board_from_moves(p).game_over]
+    tasks = []
+    for i, (p, t) in enumerate(live):
+        n = len(p)
+        mover = 1 + (n % 2)
+        ai_player = mover if i % 4 else 3 - mover          # mostly the natural mover, sometimes not
+        if n >= 150:      # late game: E+1 < S so the UCB scan runs at the root and below
+            tasks.append((p, ai_player, 200 if i % 2 else 100, 1.8 if i % 2 else 1.6, 0.2, 0, "hard"))
+        elif n >= 90:
+            tasks.append((p, ai_player, 160, 1.6, 0.2, 0, "medium"))
+        elif n >= 40 and i % 2 == 0:
+            tasks.append((p, ai_player, 40, 1.2, 0.2, 0, "easy"))
+        elif i % 3 == 0:
+            tasks.append((p, ai_player, 12, 1.8, 0.2, 0, "hard"))
+    # a few with beta = 0 and a large beta, to separate the UCB term from the BG bonus
+    dense = [p for p, t in live if t == "dense" and len(p) >= 170]
+    tasks.append((dense[0], 1, 150, 1.6, 0.0, 0, "medium"))
+    tasks.append((dense[1], 2, 150, 1.6, 5.0, 0, "medium"))
+    tasks.append((dense[2], 1, 400, 1.8, 0.2, 0, "hard"))
+    tasks.sort(key=lambda t: -t[2] * (226 - len(t[0])))
+    recs = pool.map(_mcts_task, tasks, chunksize=1)
+    _save_trees(recs, os.path.join(outdir, "mcts.npz"))
+    print("mcts:", len(recs), "cpu-seconds", sum(r["seconds"] for r in recs))
+
+
+# ----------------------------------------------------------------------------- part: planner (DET-B)
+def _planner_task(args):
+    seq, ai_player, difficulty = args
+    b = board_from_moves(seq)
+    if b.game_over:
+        return None
+    det_patch()
+    pl = bg_planner.BGPlannerAI(ai_player, difficulty, device="cpu")
+    load_weights(pl.graph_net, "graphnet")
+    load_weights(pl.opp_dqn, "dqn")
+    ks = pl.k_search
+    scores = np.full(225, np.nan, np.float64)
+    for (r, c) in b.get_valid_moves():
+        scores[r * 15 + c] = ks.score_move(b, (r, c), ai_player)
+    k = pl.params["k"]
+    top = ks.top_k_moves(b, ai_player, k=k)
+    topi = np.full(16, -1, np.int32)
+    topi[:len(top)] = [r * 15 + c for r, c in top]
+    planes = pl._board_to_planes(b.get_board_state())
+    x = torch.from_numpy(planes).unsqueeze(0)
+    with torch.no_grad():
+        logits = pl.graph_net(x).squeeze(0)
+        policy = torch.softmax(logits, dim=0).numpy()
+        q = pl.opp_dqn(x).squeeze(0).numpy()
+    a = pl.params["mix_alpha"]
+    composed = np.full(16, np.nan, np.float64)
+    for j, (r, c) in enumerate(top):
+        composed[j] = a * float(policy[r * 15 + c]) - (1 - a) * float(q[r * 15 + c])
+    mv = pl.get_move(b)
+    det_unpatch()
+    return dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(),
+                ai_player=ai_player, difficulty=difficulty, k=k, scores=scores, topk=topi,
+                gn_logits=logits.numpy().astype(np.float32), gn_policy=policy.astype(np.float32),
+                dqn_q=q.astype(np.float32), composed=composed, move=mv[0] * 15 + mv[1])
+
+
+def part_planner(pool, outdir):
+    pos, tags = load_positions(outdir)
+    tasks = []
+    for i, p in enumerate(pos):
+        tasks.append((p, 1 + (i % 2), ("hard", "medium", "easy")[i % 3]))
+        if tags[i] == "tactical":
+            tasks.append((p, 2 - (i % 2), "hard"))
+    recs = [r for r in pool.map(_planner_task, tasks, chunksize=2) if r is not None]
+    out = {k: np.stack([np.asarray(r[k]) for r in recs]) for k in recs[0]}
+    np.savez_compressed(os.path.join(outdir, "planner.npz"), **out)
+    print("planner:", len(recs))
+
+
+# ----------------------------------------------------------------------------- part: nets
+def part_nets(pool, outdir):
+    pos, tags = load_positions(outdir)
+    sel = [p for p in pos][::5][:40]
+    gm = neural_network.GomokuModel(device="cpu")
+    load_weights(gm.model, "pv")
+    gn = bg_planner.GraphNet(15); load_weights(gn, "graphnet")
+    dq = bg_planner.OpponentDQN(15); load_weights(dq, "dqn")
+    rec = dict(cells=[], logits=[], value=[], probs=[], gn_logits=[], dqn_q=[], pred_value=[])
+    for p in sel:
+        b = board_from_moves(p)
+        st = b.get_board_state()
+        x = torch.from_numpy(b.get_board_tensor()).unsqueeze(0)
+        with torch.no_grad():
+            lg, v = gm.model(x)
+            rec["gn_logits"].append(gn(x).squeeze(0).numpy())
+            rec["dqn_q"].append(dq(x).squeeze(0).numpy())
+        pol, val = gm.predict(st)
+        rec["cells"].append(cells_of(b))
+        rec["logits"].append(lg.squeeze(0).numpy())
+        rec["value"].append(np.float32(v.item()))
+        rec["probs"].append(pol.astype(np.float32))
+        rec["pred_value"].append(np.float32(val))
+    np.savez_compressed(os.path.join(outdir, "nets.npz"), **{k: np.stack(v) for k, v in rec.items()})
+    print("nets:", len(sel))
+
+
+# ----------------------------------------------------------------------------- part: mctsb (DET-B)
+def part_mctsb(pool, outdir):
+    pos, tags = load_positions(outdir)
+    live = [(p, t) for p, t in zip(pos, tags) if not board_from_moves(p).game_over]
+    ro = [(p, 5 if i % 2 else 2, 1 + (i % 2)) for i, (p, t) in enumerate(live[::4])]
+    recs = [r for r in pool.map(_rollout_task, ro, chunksize=1) if r is not None]
+    out = {k: np.stack([np.asarray(r[k]) for r in recs]) for k in recs[0]}
+    np.savez_compressed(os.path.join(outdir, "rollout_planner.npz"), **out)
+    print("rollout_planner:", len(recs))
+    tasks = []
+    late = [p for p, t in live if len(p) >= 150]
+    mid = [p for p, t in live if 40 <= len(p) < 150]
+    early = [p for p, t in live if len(p) < 40]
+    for i, p in enumerate(late[:10]):
+        tasks.append((p, 1 + (len(p) % 2), 60, 1.8, 0.2, 5, "hard"))
+    for i, p in enumerate(mid[:6]):
+        tasks.append((p, 1 + (len(p) % 2), 10, 1.6, 0.2, 3, "medium"))
+    for i, p in enumerate(early[:6]):
+        tasks.append((p, 1 + (len(p) % 2), 5, 1.8, 0.2, 5, "hard"))
+    recs = pool.map(_mcts_task, tasks, chunksize=1)
+    _save_trees(recs, os.path.join(outdir, "mcts_planner.npz"))
+    print("mcts_planner:", len(recs), "cpu-seconds", sum(r["seconds"] for r in recs))
+
+
+# ----------------------------------------------------------------------------- part: stoch
+def _stoch_task(args):
+    seq, seed, n = args
+    b = board_from_moves(seq)
+    det_unpatch()
+    random.seed(seed)
+    ai = make_ai(b.current_player, "hard", planner_steps=0)
+    counts = np.zeros(4, np.int64)      # win, loss, draw, cut-off  (from the AI = mover's view)
+    steps = 0
+
+    class N:
+        board = b
+
+        @staticmethod
+        def is_terminal():
+            return False
+    orig = ai._get_terminal_value
+    last = {}
+
+    def spy(board):
+        last["mc"] = board.get_move_count()
+        return orig(board)
+    ai._get_terminal_value = spy
+    for _ in range(n):
+        v = ai._simulate(N)
+        counts[{1.0: 0, -1.0: 1, 0.1: 2, 0.0: 3}[v]] += 1
+        steps += last["mc"] - b.get_move_count()
+    return dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(),
+                counts=counts, total_steps=steps, n=n)
+
+
+def part_stoch(pool, outdir):
+    pos, tags = load_positions(outdir)
+    pick = [p for p, t in zip(pos, tags) if t in ("policy", "cluster") and 12 <= len(p) <= 60][:6]
+    pick += [p for p, t in zip(pos, tags) if t == "dense" and 120 <= len(p) <= 171][:2]
+    tasks = []
+    for i, p in enumerate(pick):
+        for s in range(4):                       # 4 shards per position -> merged below
+            tasks.append((p, 9000 + 10 * i + s, 40))
+    recs = pool.map(_stoch_task, tasks, chunksize=1)
+    merged = []
+    for i in range(len(pick)):
+        rs = recs[4 * i:4 * i + 4]
+        m = dict(rs[0])
+        m["counts"] = sum(r["counts"] for r in rs)
+        m["total_steps"] = sum(r["total_steps"] for r in rs)
+        m["n"] = sum(r["n"] for r in rs)
+        merged.append(m)
+    out = {k: np.stack([np.asarray(r[k]) for r in merged]) for k in merged[0]}
+    np.savez_compressed(os.path.join(outdir, "stoch.npz"), **out)
+    print("stoch:", len(merged))
+
+
+PARTS = dict(positions=part_positions, boards=part_boards, tiers=part_tiers, rollout=part_rollout,
+             mcts=part_mcts, planner=part_planner, nets=part_nets, mctsb=part_mctsb, stoch=part_stoch)
+
+
+def main():
+    import multiprocessing as mp
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--parts", default="all")
+    ap.add_argument("--jobs", type=int, default=os.cpu_count())
+    ap.add_argument("--out", default=HERE)
+    a = ap.parse_args()
+    parts = list(PARTS) if a.parts == "all" else a.parts.split(",")
+    with mp.get_context("fork").Pool(a.jobs, initializer=_init_board_task) as pool:
+        for p in parts:
+            t0 = time.time()
+            PARTS[p](pool, a.out)
+            print("  [%s] %.1f s" % (p, time.time() - t0), flush=True)
+
+
+if __name__ == "__main__":
+    main()

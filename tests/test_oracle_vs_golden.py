@@ -1,0 +1,108 @@
+"""Pins the C oracle (oracle/gomoku_oracle.c) against fixtures produced by the unmodified Python
+reference (tests/golden/make_goldens.py).  CPU only."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle as orc
+from conftest import golden
+
+
+def test_philox_known_answers():
+    # Random123 kat_vectors, philox4x32-10
+    L = orc.lib()
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
+        L.gzo_philox4x32_10(c, k, o)
+        assert tuple(o) == want
+
+
+def test_rules_masks_threat_pattern(oracle):
+    g = golden("boards")
+    for i in range(len(g["moves"])):
+        b = orc.board_from_moves(g["moves"][i])
+        assert np.array_equal(orc.cells_of(b), g["cells"][i])
+        assert (b.to_move, b.move_count, b.game_over, b.winner) == \
+            (g["to_move"][i], g["move_count"][i], g["game_over"][i], g["winner"][i])
+        assert np.array_equal(oracle.legal(b), g["legal"][i])
+        assert [oracle.threat(b, 1), oracle.threat(b, 2)] == list(g["threat"][i])
+        assert [oracle.pattern(b, 1), oracle.pattern(b, 2)] == [int(x) for x in g["pattern"][i]]
+        # boundary constructor: same state from the cell array alone
+        b2 = orc.board_from_cells(g["cells"][i], g["to_move"][i], g["move_count"][i])
+        assert (b2.game_over, b2.winner) == (g["game_over"][i], g["winner"][i])
+        if b.game_over:
+            continue
+        L = orc.lib()
+        for p in (1, 2):
+            for m in np.flatnonzero(g["legal"][i]):
+                t = orc.Board.from_buffer_copy(b)
+                t.to_move = p
+                L.gzo_make_move(C.byref(t), int(m) // 15, int(m) % 15)
+                st = 0 if not t.game_over else (3 if t.winner == 0 else t.winner)
+                assert st == g["status_after"][i][p - 1][m]
+                assert int(t.game_over and t.winner == p) == g["win_cells"][i][p - 1][m]
+                assert int(oracle.threat(t, p) >= 3) == g["three_cells"][i][p - 1][m]
+
+
+def test_rollout_policy_candidates(oracle):
+    g = golden("tiers")
+    for i in range(len(g["cells"])):
+        b = orc.board_from_cells(g["cells"][i], g["to_move"][i], g["move_count"][i])
+        for literal in (False, True):
+            mv, cand, fc = oracle.select_move(b, literal=literal)
+            assert mv == g["move"][i] and fc == g["from_choice"][i]
+            assert np.array_equal(cand, g["cand"][i])
+
+
+@pytest.mark.parametrize("name", ["rollout", "rollout_planner"])
+def test_det_rollouts(oracle, name):
+    g = golden(name)
+    for i in range(len(g["value"])):
+        b = orc.board_from_cells(g["start_cells"][i], g["to_move"][i], g["move_count"][i])
+        p = oracle.params(1, 1.8, 0.2, int(g["planner_steps"][i]), int(g["ai_player"][i]), "hard")
+        v, fb, st = oracle.simulate(b, p)
+        assert v == g["value"][i]
+        assert np.array_equal(orc.cells_of(fb), g["final_cells"][i])
+        assert (fb.move_count, fb.game_over, fb.winner) == \
+            (g["final_move_count"][i], g["final_game_over"][i], g["final_winner"][i])
+
+
+def test_planner_scores_topk_move(oracle):
+    g = golden("planner")
+    flips = 0
+    for i in range(len(g["cells"])):
+        b = orc.board_from_cells(g["cells"][i], g["to_move"][i], g["move_count"][i])
+        ai = int(g["ai_player"][i])
+        s = oracle.planner_scores(b, ai)
+        assert np.array_equal(np.isnan(s), np.isnan(g["scores"][i]))
+        assert np.array_equal(s[~np.isnan(s)], g["scores"][i][~np.isnan(s)])
+        p = oracle.params(1, 1.8, 0.2, 5, ai, str(g["difficulty"][i]))
+        mv, top, comp = oracle.planner_move(b, p)
+        k = int(g["k"][i])
+        assert np.array_equal(top[:16][:k], g["topk"][i][:k])
+        want = g["composed"][i][:k]
+        ok = ~np.isnan(want)
+        # planner nets are scaled up (gain 4): |q| reaches ~10, fp32 summation order gives ~3e-6 relative
+        assert np.allclose(comp[:k][ok], want[ok], rtol=0, atol=1e-4)
+        if mv != g["move"][i]:
+            # only a near-tie of the blended f32 scores may flip the pick
+            srt = np.sort(want[ok])
+            assert srt[-1] - srt[-2] < 2e-4
+            flips += 1
+    assert flips <= 2
+
+
+def test_networks(oracle):
+    g = golden("nets")
+    for i in range(len(g["cells"])):
+        lg, pr, v = oracle.pv_forward(g["cells"][i])
+        assert np.max(np.abs(lg - g["logits"][i])) < 1e-4
+        assert np.max(np.abs(pr - g["probs"][i])) < 1e-5
+        assert abs(v - g["value"][i]) < 1e-4 and abs(v - g["pred_value"][i]) < 1e-4
+        assert np.max(np.abs(oracle.graphnet_forward(g["cells"][i]) - g["gn_logits"][i])) < 1e-4
+        assert np.max(np.abs(oracle.dqn_forward(g["cells"][i]) - g["dqn_q"][i])) < 1e-4
