@@ -106,3 +106,33 @@ def test_networks(oracle):
         assert abs(v - g["value"][i]) < 1e-4 and abs(v - g["pred_value"][i]) < 1e-4
         assert np.max(np.abs(oracle.graphnet_forward(g["cells"][i]) - g["gn_logits"][i])) < 1e-4
         assert np.max(np.abs(oracle.dqn_forward(g["cells"][i]) - g["dqn_q"][i])) < 1e-4
+
+
+def _check_trees(oracle, g, allow_near_tie_flips=False):
+    bad = 0
+    for i in range(len(g["sims"])):
+        b = orc.board_from_cells(g["cells"][i], g["to_move"][i], g["move_count"][i])
+        p = oracle.params(int(g["sims"][i]), float(g["c_puct"][i]), float(g["beta"][i]),
+                          int(g["planner_steps"][i]), int(g["ai_player"][i]), str(g["difficulty"][i]))
+        t = oracle.search(b, p)
+        n = int(g["n_nodes"][i])
+        same = (len(t["parent"]) == n and np.array_equal(t["parent"], g["parent"][i][:n])
+                and np.array_equal(t["move"], g["move"][i][:n])
+                and np.array_equal(t["visits"], g["visits"][i][:n])
+                and np.array_equal(t["value"], g["value"][i][:n])          # bit-exact float64 sums
+                and t["stats"].best_move == g["best_move"][i])
+        if not same:
+            bad += 1
+            assert allow_near_tie_flips, "tree %d differs" % i
+    return bad
+
+
+def test_mcts_det_a_whole_trees(oracle):
+    """DET-A (planner_steps=0): every node of every tree, bit-exact."""
+    assert _check_trees(oracle, golden("mcts")) == 0
+
+
+def test_mcts_det_b_whole_trees(oracle):
+    """DET-B (planner-guided playouts).  The blended f32 pick may flip on a near-tie."""
+    g = golden("mcts_planner")
+    assert _check_trees(oracle, g, allow_near_tie_flips=True) <= 1
