@@ -1,0 +1,562 @@
+// gz_api.cu -- C ABI of libgomoku_b200.so (include/gomoku_b200.h): handle life cycle, weight
+// packing (BatchNorm folding, layout change), and the host-side wave scheduler that advances all
+// trees one simulation at a time.  No CPU compute path exists here: every entry point that does
+// work launches kernels and fails with GZ_ERR_CUDA when there is no device.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "gz_engine.h"
+
+using namespace gz;
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char *fmt, const char *a = "", const char *b = "") {
+    snprintf(g_err, sizeof g_err, fmt, a, b);
+    return code;
+}
+#define CK(call)                                                                             \
+    do {                                                                                     \
+        cudaError_t _e = (call);                                                             \
+        if (_e != cudaSuccess) return fail(GZ_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_e)); \
+    } while (0)
+#define CKL()                                                                                \
+    do {                                                                                     \
+        cudaError_t _e = cudaGetLastError();                                                 \
+        if (_e != cudaSuccess) return fail(GZ_ERR_CUDA, "kernel launch: %s%s", cudaGetErrorString(_e)); \
+    } while (0)
+
+extern "C" const char *gz_last_error(void) { return g_err; }
+extern "C" int gz_version(void) { return 100; }
+
+extern "C" int64_t gz_pv_param_count(void) {
+    return 3456 + 128 + 512 + 2 * (2 * (147456 + 128) + 2 * 512) + 256 + 2 + 101250 + 225 + 128 + 1 +
+           14400 + 64 + 64 + 1;
+}
+extern "C" int64_t gz_graphnet_param_count(void) {
+    return 64 * 27 + 64 + 4 * (64 * 64 * 9 + 64 + 64 * 64 + 64) + 128 + 2 + 101250 + 225;
+}
+extern "C" int64_t gz_dqn_param_count(void) { return 256 * 675 + 256 + 256 * 256 + 256 + 225 * 256 + 225; }
+
+template <typename T>
+static cudaError_t dalloc(T **p, size_t n) {
+    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T));
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, n * sizeof(T));
+    return e;
+}
+
+extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
+    if (!cfg || !out) return fail(GZ_ERR_ARG, "gz_create: null argument");
+    if (cfg->max_games < 1 || cfg->max_simulations < 1 || cfg->max_simulations > 32000)
+        return fail(GZ_ERR_ARG, "gz_create: max_games/max_simulations out of range");
+    int ndev = 0;
+    cudaError_t e0 = cudaGetDeviceCount(&ndev);
+    if (e0 != cudaSuccess || ndev == 0)
+        return fail(GZ_ERR_CUDA, "gz_create: no CUDA device (%s); this library has no CPU path",
+                    cudaGetErrorString(e0));
+    CK(cudaSetDevice(cfg->device));
+    Engine *e = new Engine();
+    memset(e, 0, sizeof *e);
+    e->cfg = *cfg;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    e->sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking));
+    const size_t G = cfg->max_games, cap = (size_t)cfg->max_simulations + 1, N = G * cap;
+    TreeArrays &t = e->tree;
+    t.cap = (int32_t)cap;
+    CK(dalloc(&t.parent, N)); CK(dalloc(&t.move, N)); CK(dalloc(&t.status, N));
+    CK(dalloc(&t.nchild, N)); CK(dalloc(&t.nempty, N)); CK(dalloc(&t.visits, N));
+    CK(dalloc(&t.value, N)); CK(dalloc(&t.bgb, N)); CK(dalloc(&t.vhead, N));
+    if (cfg->store_priors) CK(dalloc(&t.prior, N * kCells));
+    CK(dalloc(&t.n_nodes, G)); CK(dalloc(&t.root, G)); CK(dalloc(&t.ai_player, G));
+    SimArrays &s = e->sim;
+    CK(dalloc(&s.board, G)); CK(dalloc(&s.leaf, G)); CK(dalloc(&s.need_eval, G));
+    CK(dalloc(&s.steps, G)); CK(dalloc(&s.value, G)); CK(dalloc(&s.topk, G * kMaxTopK));
+    CK(dalloc(&s.ntop, G));
+    for (int i = 0; i < 3; ++i) CK(dalloc(&e->act[i], G * 128 * kCells));
+    CK(dalloc(&e->gn_logits, G * kCells)); CK(dalloc(&e->gn_policy, G * kCells));
+    CK(dalloc(&e->dqn_q, G * kCells));
+    CK(dalloc(&e->pv_logits, G * kCells)); CK(dalloc(&e->pv_probs, G * kCells));
+    CK(dalloc(&e->pv_value, G));
+    CK(dalloc(&e->tmp_boards, G));
+    CK(dalloc(&e->tmp_u8, G * 232));
+    CK(dalloc(&e->io_cv, G * kCells)); CK(dalloc(&e->io_cval, G * kCells)); CK(dalloc(&e->io_best, G));
+    CK(dalloc(&e->counters, 8));
+    CK(dalloc(&e->log_table, kLogTableMax));
+    CK(dalloc(&e->tanh_table, kTanhTableMax));
+    *out = reinterpret_cast<gz_handle>(e);
+    return GZ_OK;
+}
+
+extern "C" int gz_destroy(gz_handle h) {
+    if (!h) return GZ_OK;
+    Engine *e = reinterpret_cast<Engine *>(h);
+    cudaSetDevice(e->cfg.device);
+    cudaDeviceSynchronize();
+    TreeArrays &t = e->tree;
+    void *ptrs[] = {t.parent, t.move, t.status, t.nchild, t.nempty, t.visits, t.value, t.bgb, t.vhead,
+                    t.prior, t.n_nodes, t.root, t.ai_player, e->sim.board, e->sim.leaf,
+                    e->sim.need_eval, e->sim.steps, e->sim.value, e->sim.topk, e->sim.ntop, e->act[0],
+                    e->act[1], e->act[2], e->gn_logits, e->gn_policy, e->dqn_q, e->pv_logits,
+                    e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
+                    e->tanh_table, e->weight_blob, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    cudaStreamDestroy(e->own_stream);
+    delete e;
+    return GZ_OK;
+}
+
+// ---- weight packing ---------------------------------------------------------------------------
+namespace {
+struct Packer {
+    std::vector<float> host;
+    size_t take(size_t n) {  // 64-float (256 B) aligned slots
+        size_t o = host.size();
+        host.resize(o + ((n + 63) / 64) * 64, 0.f);
+        return o;
+    }
+};
+
+// conv weight [cout][cin][k][k] (+ optional BN [w,b,mean,var]) -> [cin][tap][cout], folded bias
+void pack_conv(Packer &pk, const float *w, const float *b, const float *bn, int cout, int cin, int k,
+               size_t &ow, size_t &ob) {
+    int T = k * k;
+    ow = pk.take((size_t)cin * T * cout);
+    ob = pk.take(cout);
+    for (int co = 0; co < cout; ++co) {
+        double scale = 1.0, shift = 0.0;
+        if (bn) {
+            scale = (double)bn[co] / sqrt((double)bn[3 * cout + co] + 1e-5);
+            shift = (double)bn[cout + co] - (double)bn[2 * cout + co] * scale;
+        }
+        for (int ci = 0; ci < cin; ++ci)
+            for (int t = 0; t < T; ++t)
+                pk.host[ow + ((size_t)ci * T + t) * cout + co] =
+                    (float)((double)w[((size_t)co * cin + ci) * T + t] * scale);
+        pk.host[ob + co] = (float)((double)b[co] * scale + shift);
+    }
+}
+// linear weight [out][in] -> [in][out]
+void pack_linear_t(Packer &pk, const float *w, const float *b, int nout, int nin, size_t &ow, size_t &ob) {
+    ow = pk.take((size_t)nin * nout);
+    ob = pk.take(nout);
+    for (int o = 0; o < nout; ++o) {
+        for (int i = 0; i < nin; ++i) pk.host[ow + (size_t)i * nout + o] = w[(size_t)o * nin + i];
+        pk.host[ob + o] = b[o];
+    }
+}
+// 1x1 head conv [cout][cin] -> [cin][cout]
+void pack_head_conv(Packer &pk, const float *w, const float *b, int cout, int cin, size_t &ow, size_t &ob) {
+    pack_linear_t(pk, w, b, cout, cin, ow, ob);
+}
+}  // namespace
+
+static int upload(Packer &pk, float **dev) {
+    if (*dev) { cudaFree(*dev); *dev = nullptr; }
+    CK(cudaMalloc((void **)dev, pk.host.size() * sizeof(float)));
+    CK(cudaMemcpy(*dev, pk.host.data(), pk.host.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return GZ_OK;
+}
+
+extern "C" int gz_set_pv_weights(gz_handle h, const float *f, int64_t n) {
+    if (!h || !f) return fail(GZ_ERR_ARG, "gz_set_pv_weights: null argument");
+    if (n != gz_pv_param_count()) return fail(GZ_ERR_ARG, "gz_set_pv_weights: wrong parameter count");
+    Engine *e = reinterpret_cast<Engine *>(h);
+    CK(cudaSetDevice(e->cfg.device));
+    Packer pk;
+    size_t o[32];
+    const float *p = f;
+    pack_conv(pk, p, p + 3456, p + 3456 + 128, 128, 3, 3, o[0], o[1]);
+    p += 3456 + 128 + 512;
+    for (int blk = 0; blk < 2; ++blk) {
+        const float *c1w = p, *c1b = p + 147456, *c2w = c1b + 128, *c2b = c2w + 147456;
+        const float *bn1 = c2b + 128, *bn2 = bn1 + 512;
+        pack_conv(pk, c1w, c1b, bn1, 128, 128, 3, o[2 + 4 * blk], o[3 + 4 * blk]);
+        pack_conv(pk, c2w, c2b, bn2, 128, 128, 3, o[4 + 4 * blk], o[5 + 4 * blk]);
+        p = bn2 + 512;
+    }
+    pack_head_conv(pk, p, p + 256, 2, 128, o[10], o[11]); p += 256 + 2;
+    pack_linear_t(pk, p, p + 101250, 225, 450, o[12], o[13]); p += 101250 + 225;
+    pack_head_conv(pk, p, p + 128, 1, 128, o[14], o[15]); p += 128 + 1;
+    pack_linear_t(pk, p, p + 14400, 64, 225, o[16], o[17]); p += 14400 + 64;
+    size_t ow2 = pk.take(64), ob2 = pk.take(1);
+    memcpy(&pk.host[ow2], p, 64 * sizeof(float));
+    pk.host[ob2] = p[64];
+    float *d = e->pv.conv0.w;   // base of the previous PV blob (if any)
+    int rc = upload(pk, &d);
+    if (rc) return rc;
+    PvWeights &w = e->pv;
+    w.conv0 = {d + o[0], d + o[1]};
+    for (int i = 0; i < 4; ++i) w.tower[i] = {d + o[2 + 2 * i], d + o[3 + 2 * i]};
+    w.pconv_w = d + o[10]; w.pconv_b = d + o[11];
+    w.pfc_wt = d + o[12]; w.pfc_b = d + o[13];
+    w.vconv_w = d + o[14]; w.vconv_b = d + o[15];
+    w.vfc1_wt = d + o[16]; w.vfc1_b = d + o[17];
+    w.vfc2_w = d + ow2; w.vfc2_b = d + ob2;
+    e->have_pv = true;
+    return GZ_OK;
+}
+
+extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn, const float *dqf,
+                                      int64_t ndq) {
+    if (!h || !gnf || !dqf) return fail(GZ_ERR_ARG, "gz_set_planner_weights: null argument");
+    if (ngn != gz_graphnet_param_count() || ndq != gz_dqn_param_count())
+        return fail(GZ_ERR_ARG, "gz_set_planner_weights: wrong parameter count");
+    Engine *e = reinterpret_cast<Engine *>(h);
+    CK(cudaSetDevice(e->cfg.device));
+    {
+        Packer pk;
+        size_t o[24];
+        const float *p = gnf;
+        pack_conv(pk, p, p + 1728, nullptr, 64, 3, 3, o[0], o[1]); p += 1728 + 64;
+        for (int i = 0; i < 4; ++i) {
+            pack_conv(pk, p, p + 36864, nullptr, 64, 64, 3, o[2 + 4 * i], o[3 + 4 * i]); p += 36864 + 64;
+            pack_conv(pk, p, p + 4096, nullptr, 64, 64, 1, o[4 + 4 * i], o[5 + 4 * i]); p += 4096 + 64;
+        }
+        pack_head_conv(pk, p, p + 128, 2, 64, o[18], o[19]); p += 128 + 2;
+        pack_linear_t(pk, p, p + 101250, 225, 450, o[20], o[21]);
+        float *d = e->gn.embed.w;
+        int rc = upload(pk, &d);
+        if (rc) return rc;
+        GraphNetWeights &w = e->gn;
+        w.embed = {d + o[0], d + o[1]};
+        for (int i = 0; i < 4; ++i) {
+            w.l3[i] = {d + o[2 + 4 * i], d + o[3 + 4 * i]};
+            w.l1[i] = {d + o[4 + 4 * i], d + o[5 + 4 * i]};
+        }
+        w.hconv_w = d + o[18]; w.hconv_b = d + o[19];
+        w.hfc_wt = d + o[20]; w.hfc_b = d + o[21];
+    }
+    {
+        Packer pk;
+        size_t o[6];
+        const float *p = dqf;
+        pack_linear_t(pk, p, p + 256 * 675, 256, 675, o[0], o[1]); p += 256 * 675 + 256;
+        pack_linear_t(pk, p, p + 65536, 256, 256, o[2], o[3]); p += 65536 + 256;
+        pack_linear_t(pk, p, p + 225 * 256, 225, 256, o[4], o[5]);
+        float *d = e->dqn.w1t;
+        int rc = upload(pk, &d);
+        if (rc) return rc;
+        e->dqn = {d + o[0], d + o[1], d + o[2], d + o[3], d + o[4], d + o[5]};
+    }
+    e->have_planner = true;
+    return GZ_OK;
+}
+
+extern "C" int gz_set_tables(gz_handle h, const double *hl, int32_t nl, const double *ht, int32_t nt) {
+    if (!h) return fail(GZ_ERR_ARG, "gz_set_tables: null handle");
+    Engine *e = reinterpret_cast<Engine *>(h);
+    CK(cudaSetDevice(e->cfg.device));
+    if (nl > kLogTableMax) nl = kLogTableMax;
+    if (nt > kTanhTableMax) nt = kTanhTableMax;
+    if (hl && nl > 0) CK(cudaMemcpy(e->log_table, hl, nl * sizeof(double), cudaMemcpyHostToDevice));
+    if (ht && nt > 0) CK(cudaMemcpy(e->tanh_table, ht, nt * sizeof(double), cudaMemcpyHostToDevice));
+    e->n_log = hl ? nl : 0;
+    e->n_tanh = ht ? nt : 0;
+    return GZ_OK;
+}
+
+// ---- helpers -------------------------------------------------------------------------------------
+static inline Engine *eng(gz_handle h) { return reinterpret_cast<Engine *>(h); }
+static inline cudaStream_t strm(void *s) { return reinterpret_cast<cudaStream_t>(s); }
+
+static int check_batch(Engine *e, int G, const char *who) {
+    if (!e) return fail(GZ_ERR_ARG, "%s: null handle", who);
+    if (G < 1 || G > e->cfg.max_games) return fail(GZ_ERR_ARG, "%s: G out of range (max_games)", who);
+    cudaError_t ce = cudaSetDevice(e->cfg.device);
+    if (ce != cudaSuccess) return fail(GZ_ERR_CUDA, "%s: %s", who, cudaGetErrorString(ce));
+    return GZ_OK;
+}
+
+static SearchCfg make_cfg(const gz_search_params *p) {
+    SearchCfg c;
+    c.S = p->num_simulations;
+    c.planner_steps = p->planner_steps < 0 ? 0 : p->planner_steps;
+    c.planner_k = p->planner_k;
+    c.deterministic = p->deterministic;
+    c.eval_nodes = p->eval_nodes;
+    c.c_puct = p->c_puct;
+    c.beta = p->beta;
+    c.alpha = p->planner_alpha;
+    c.explore = p->planner_explore;
+    c.seed_lo = (uint32_t)(p->seed & 0xFFFFFFFFull);
+    c.seed_hi = (uint32_t)(p->seed >> 32);
+    c.game_base = p->game_base;
+    return c;
+}
+
+// ---- boards --------------------------------------------------------------------------------------
+extern "C" int gz_boards_from_cells(gz_handle h, const uint8_t *d_cells, const uint8_t *d_to_move,
+                                    const uint16_t *d_mc, int32_t G, gz_board *d_boards, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_boards_from_cells");
+    if (rc) return rc;
+    if (!d_cells || !d_to_move || !d_mc || !d_boards) return fail(GZ_ERR_ARG, "gz_boards_from_cells: null pointer");
+    launch_boards_from_cells(d_cells, d_to_move, d_mc, G, d_boards, strm(stream));
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_boards_to_cells(gz_handle h, const gz_board *d_boards, int32_t G, uint8_t *d_cells,
+                                  void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_boards_to_cells");
+    if (rc) return rc;
+    if (!d_boards || !d_cells) return fail(GZ_ERR_ARG, "gz_boards_to_cells: null pointer");
+    launch_boards_to_cells(d_boards, G, d_cells, strm(stream));
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_make_moves(gz_handle h, gz_board *d_boards, const int32_t *d_moves, int32_t G,
+                             uint8_t *d_ok, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_make_moves");
+    if (rc) return rc;
+    if (!d_boards || !d_moves) return fail(GZ_ERR_ARG, "gz_make_moves: null pointer");
+    launch_make_moves(d_boards, d_moves, G, d_ok, strm(stream));
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_board_ops(gz_handle h, const gz_board *d_boards, int32_t G, uint32_t *d_legal,
+                            uint32_t *d_win, uint32_t *d_three, int32_t *d_threat, int64_t *d_pattern,
+                            void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_board_ops");
+    if (rc) return rc;
+    if (!d_boards) return fail(GZ_ERR_ARG, "gz_board_ops: null pointer");
+    launch_board_ops(d_boards, G, d_legal, d_win, d_three, d_threat, d_pattern, strm(stream));
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
+// ---- networks ------------------------------------------------------------------------------------
+extern "C" int gz_pv_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_logits,
+                             float *d_probs, float *d_value, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_pv_forward");
+    if (rc) return rc;
+    if (!d_boards) return fail(GZ_ERR_ARG, "gz_pv_forward: null pointer");
+    if (!e->have_pv) return fail(GZ_ERR_STATE, "gz_pv_forward: gz_set_pv_weights was not called");
+    nn_pv_forward_fp32(*e, d_boards, nullptr, G, d_logits, d_probs, d_value, nullptr, nullptr, strm(stream));
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, int32_t G,
+                                       float *d_gn_logits, float *d_gn_policy, float *d_dqn_q,
+                                       void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_planner_nets_forward");
+    if (rc) return rc;
+    if (!d_boards) return fail(GZ_ERR_ARG, "gz_planner_nets_forward: null pointer");
+    if (!e->have_planner) return fail(GZ_ERR_STATE, "gz_planner_nets_forward: planner weights not set");
+    nn_planner_forward_fp32(*e, d_boards, G, d_gn_logits ? d_gn_logits : e->gn_logits,
+                            d_gn_policy ? d_gn_policy : e->gn_policy, d_dqn_q ? d_dqn_q : e->dqn_q,
+                            strm(stream));
+    CKL();
+    return GZ_OK;
+}
+
+// ---- planner move --------------------------------------------------------------------------------
+extern "C" int gz_planner_move(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player,
+                               int32_t G, const gz_search_params *p, int32_t sim, int32_t step,
+                               int64_t *d_scores2, int32_t *d_topk, double *d_composed, int32_t *d_move,
+                               void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_planner_move");
+    if (rc) return rc;
+    if (!d_boards || !d_ai_player || !p) return fail(GZ_ERR_ARG, "gz_planner_move: null pointer");
+    if (!e->have_planner) return fail(GZ_ERR_STATE, "gz_planner_move: planner weights not set");
+    SearchCfg c = make_cfg(p);
+    cudaStream_t s = strm(stream);
+    int32_t *topk = d_topk ? d_topk : e->sim.topk;
+    launch_planner_score(d_boards, d_ai_player, nullptr, G, c, step, topk, e->sim.ntop, d_scores2, s);
+    nn_planner_forward_fp32(*e, d_boards, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+    launch_planner_pick(const_cast<gz_board *>(d_boards), d_ai_player, nullptr, G, c, sim, step, topk,
+                        e->sim.ntop, e->gn_policy, e->dqn_q, d_composed, d_move, false, nullptr, s);
+    e->launches += 2;
+    CKL();
+    return GZ_OK;
+}
+
+// ---- rollout -------------------------------------------------------------------------------------
+extern "C" int gz_rollout_policy(gz_handle h, const gz_board *d_boards, int32_t G,
+                                 const gz_search_params *p, int32_t sim, int32_t step, int32_t *d_move,
+                                 uint32_t *d_cand, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_rollout_policy");
+    if (rc) return rc;
+    if (!d_boards || !p || !d_move) return fail(GZ_ERR_ARG, "gz_rollout_policy: null pointer");
+    launch_rollout_policy(d_boards, G, make_cfg(p), sim, step, d_move, d_cand, strm(stream));
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
+// planner prefix + tail on e->sim.board / e->sim.steps (already initialised by the caller)
+static void run_playouts(Engine *e, int G, const SearchCfg &c, int sim, cudaStream_t s) {
+    for (int k = 0; k < c.planner_steps; ++k) {
+        launch_planner_score(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, k, e->sim.topk,
+                             e->sim.ntop, nullptr, s);
+        nn_planner_forward_fp32(*e, e->sim.board, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+        launch_planner_pick(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, sim, -1, e->sim.topk,
+                            e->sim.ntop, e->gn_policy, e->dqn_q, nullptr, nullptr, true, e->counters, s);
+        e->launches += 2;
+    }
+    launch_rollout_tail(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, sim, e->sim.value,
+                        e->counters, s);
+    e->launches += 1;
+}
+
+extern "C" int gz_rollout(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player, int32_t G,
+                          const gz_search_params *p, int32_t sim, double *d_value, int32_t *d_steps,
+                          gz_board *d_final, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_rollout");
+    if (rc) return rc;
+    if (!d_boards || !d_ai_player || !p) return fail(GZ_ERR_ARG, "gz_rollout: null pointer");
+    SearchCfg c = make_cfg(p);
+    if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_rollout: planner weights not set");
+    cudaStream_t s = strm(stream);
+    CK(cudaMemcpyAsync(e->sim.board, d_boards, sizeof(gz_board) * G, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(e->tree.ai_player, d_ai_player, G, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemsetAsync(e->sim.steps, 0, sizeof(int32_t) * G, s));
+    run_playouts(e, G, c, sim, s);
+    if (d_value) CK(cudaMemcpyAsync(d_value, e->sim.value, sizeof(double) * G, cudaMemcpyDeviceToDevice, s));
+    if (d_steps) CK(cudaMemcpyAsync(d_steps, e->sim.steps, sizeof(int32_t) * G, cudaMemcpyDeviceToDevice, s));
+    if (d_final) CK(cudaMemcpyAsync(d_final, e->sim.board, sizeof(gz_board) * G, cudaMemcpyDeviceToDevice, s));
+    CKL();
+    return GZ_OK;
+}
+
+// ---- search --------------------------------------------------------------------------------------
+static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_ai, int G,
+                         const gz_search_params *p, int32_t *d_cv, double *d_cval, int32_t *d_best,
+                         cudaStream_t s) {
+    SearchCfg c = make_cfg(p);
+    if (c.S < 1 || c.S > e->cfg.max_simulations) return fail(GZ_ERR_ARG, "gz_search: num_simulations out of range");
+    if (c.eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_search: gz_set_pv_weights was not called");
+    if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_search: planner weights not set");
+    launch_tree_init(*e, d_boards, d_ai, G, s);
+    e->launches += 1;
+    if (c.eval_nodes)
+        nn_pv_forward_fp32(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
+                           e->tree.prior, e->sim.leaf, s);
+    for (int sim = 0; sim < c.S; ++sim) {
+        launch_tree_step(*e, G, c, sim, s);
+        e->launches += 1;
+        if (c.eval_nodes)
+            nn_pv_forward_fp32(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
+                               e->tree.prior, e->sim.leaf, s);
+        run_playouts(e, G, c, sim, s);
+    }
+    launch_tree_step(*e, G, c, c.S, s);   // backs up the last simulation
+    launch_tree_finalize(*e, G, c, d_cv, d_cval, d_best, s);
+    e->launches += 2;
+    CKL();
+    e->searched = true;
+    return GZ_OK;
+}
+
+extern "C" int gz_search(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player, int32_t G,
+                         const gz_search_params *p, int32_t *d_child_visits, double *d_child_value,
+                         int32_t *d_best_move, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_search");
+    if (rc) return rc;
+    if (!d_boards || !d_ai_player || !p) return fail(GZ_ERR_ARG, "gz_search: null pointer");
+    rc = search_device(e, d_boards, d_ai_player, G, p, d_child_visits, d_child_value, d_best_move, strm(stream));
+    if (rc) return rc;
+    unsigned long long add = (unsigned long long)G * (unsigned long long)p->num_simulations;
+    (void)add;
+    return GZ_OK;
+}
+
+extern "C" int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t *h_to_move,
+                              const uint16_t *h_mc, const uint8_t *h_ai, int32_t G,
+                              const gz_search_params *p, int32_t *h_cv, double *h_cval, int32_t *h_best) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_search_host");
+    if (rc) return rc;
+    if (!h_cells || !h_to_move || !h_mc || !h_ai || !p) return fail(GZ_ERR_ARG, "gz_search_host: null pointer");
+    cudaStream_t s = e->own_stream;
+    uint8_t *d_cells = e->tmp_u8, *d_tm = e->tmp_u8 + (size_t)225 * e->cfg.max_games;
+    uint8_t *d_ai = d_tm + e->cfg.max_games;
+    uint16_t *d_mc = reinterpret_cast<uint16_t *>(e->tmp_u8 + (size_t)228 * e->cfg.max_games);
+    CK(cudaMemcpyAsync(d_cells, h_cells, (size_t)G * kCells, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_tm, h_to_move, G, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_ai, h_ai, G, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_mc, h_mc, (size_t)G * 2, cudaMemcpyHostToDevice, s));
+    launch_boards_from_cells(d_cells, d_tm, d_mc, G, e->tmp_boards, s);
+    e->launches += 1;
+    rc = search_device(e, e->tmp_boards, d_ai, G, p, e->io_cv, e->io_cval, e->io_best, s);
+    if (rc) return rc;
+    if (h_cv) CK(cudaMemcpyAsync(h_cv, e->io_cv, sizeof(int32_t) * G * kCells, cudaMemcpyDeviceToHost, s));
+    if (h_cval) CK(cudaMemcpyAsync(h_cval, e->io_cval, sizeof(double) * G * kCells, cudaMemcpyDeviceToHost, s));
+    if (h_best) CK(cudaMemcpyAsync(h_best, e->io_best, sizeof(int32_t) * G, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return GZ_OK;
+}
+
+extern "C" int gz_get_tree(gz_handle h, int32_t g, int32_t cap, int32_t *h_parent, int32_t *h_move,
+                           int32_t *h_visits, double *h_value, int32_t *n_nodes) {
+    Engine *e = eng(h);
+    if (!e || !n_nodes) return fail(GZ_ERR_ARG, "gz_get_tree: null argument");
+    if (!e->searched) return fail(GZ_ERR_STATE, "gz_get_tree: no search has run on this handle");
+    if (g < 0 || g >= e->cfg.max_games) return fail(GZ_ERR_ARG, "gz_get_tree: game index out of range");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    int nn = 0;
+    CK(cudaMemcpy(&nn, e->tree.n_nodes + g, sizeof(int), cudaMemcpyDeviceToHost));
+    *n_nodes = nn;
+    int n = nn < cap ? nn : cap;
+    size_t o = (size_t)g * e->tree.cap;
+    std::vector<int16_t> par(n);
+    std::vector<uint8_t> mv(n);
+    CK(cudaMemcpy(par.data(), e->tree.parent + o, n * sizeof(int16_t), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(mv.data(), e->tree.move + o, n, cudaMemcpyDeviceToHost));
+    if (h_visits) CK(cudaMemcpy(h_visits, e->tree.visits + o, n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    if (h_value) CK(cudaMemcpy(h_value, e->tree.value + o, n * sizeof(double), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; ++i) {
+        if (h_parent) h_parent[i] = par[i];
+        if (h_move) h_move[i] = i == 0 ? -1 : (mv[i] >> 4) * 15 + (mv[i] & 15);
+    }
+    return GZ_OK;
+}
+
+extern "C" int gz_get_counters(gz_handle h, gz_counters *out) {
+    Engine *e = eng(h);
+    if (!e || !out) return fail(GZ_ERR_ARG, "gz_get_counters: null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    unsigned long long c[8];
+    CK(cudaMemcpy(c, e->counters, sizeof c, cudaMemcpyDeviceToHost));
+    out->nodes_created = (int64_t)c[1];
+    out->pv_evals = (int64_t)c[2];
+    out->planner_steps = (int64_t)c[3];
+    out->rollout_steps = (int64_t)c[4];
+    out->terminal_leaves = (int64_t)c[5];
+    out->simulations = (int64_t)c[0];
+    out->kernel_launches = e->launches;
+    return GZ_OK;
+}
+
+extern "C" int gz_reset_counters(gz_handle h) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_reset_counters: null handle");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemset(e->counters, 0, 8 * sizeof(unsigned long long)));
+    e->launches = 0;
+    return GZ_OK;
+}

@@ -1,0 +1,149 @@
+// gz_engine.h -- internal state of one engine handle and the kernel launchers (one per .cu file).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gomoku_b200.h"
+
+namespace gz {
+
+constexpr int kCells = 225;
+constexpr int kMaxTopK = 16;
+constexpr int kLogTableMax = 2048;
+constexpr int kTanhTableMax = 4096;
+
+// fp32 network parameters on the device, BN folded, laid out for the FFMA kernels:
+// conv weights as [cin][tap][cout] (cout contiguous), linear weights transposed to [in][out].
+struct ConvW {
+    float *w;  // [cin*taps][cout]
+    float *b;  // [cout]
+};
+struct PvWeights {
+    ConvW conv0;         // 3 -> 128, 3x3 (+bn)
+    ConvW tower[4];      // block0.conv1, block0.conv2, block1.conv1, block1.conv2 (+bn each)
+    float *pconv_w, *pconv_b;   // [128][2], [2]
+    float *pfc_wt, *pfc_b;      // [450][225], [225]
+    float *vconv_w, *vconv_b;   // [128], [1]
+    float *vfc1_wt, *vfc1_b;    // [225][64], [64]
+    float *vfc2_w, *vfc2_b;     // [64], [1]
+};
+struct GraphNetWeights {
+    ConvW embed;         // 3 -> 64, 3x3
+    ConvW l3[4];         // 64 -> 64, 3x3
+    ConvW l1[4];         // 64 -> 64, 1x1
+    float *hconv_w, *hconv_b;   // [64][2], [2]
+    float *hfc_wt, *hfc_b;      // [450][225], [225]
+};
+struct DqnWeights {
+    float *w1t, *b1;     // [675][256]
+    float *w2t, *b2;     // [256][256]
+    float *w3t, *b3;     // [256][225]
+};
+
+// Flat SoA tree storage, tree g owns slots [g*cap, (g+1)*cap); node 0 is the root.
+struct TreeArrays {
+    int32_t cap;          // max_simulations + 1
+    int16_t *parent;      // -1 for the root
+    uint8_t *move;        // bit position 16*r+c of the move leading here
+    uint8_t *status;      // 0 live, 1/2 winner, 3 draw
+    int16_t *nchild;      // children created so far
+    int16_t *nempty;      // empty cells of the node's board = len(unexplored) at creation
+    int32_t *visits;
+    double *value;
+    double *bgb;          // beta * tanh(pattern_score/1e4)
+    float *vhead;         // value head output of the node (never read by the search, like the reference)
+    float *prior;         // optional [cap][225] renormalised priors (MCTSNode.prior_prob)
+    int32_t *n_nodes;     // per tree
+    gz_board *root;       // per tree
+    uint8_t *ai_player;   // per tree
+};
+
+// Per-simulation state of every game (one simulation in flight per tree).
+struct SimArrays {
+    gz_board *board;      // leaf board, then the rollout board
+    int32_t *leaf;        // node index of the leaf
+    uint8_t *need_eval;   // leaf was created in this wave and is not terminal
+    int32_t *steps;       // rollout steps taken so far (planner steps included)
+    double *value;        // rollout result
+    // planner scratch
+    int32_t *topk;        // [G][16]
+    int32_t *ntop;        // [G]
+    int64_t *scores2;     // [G][225] (only when requested)
+};
+
+struct Engine {
+    gz_config cfg;
+    int sm_count;
+    cudaStream_t own_stream;
+    bool have_pv, have_planner;
+    PvWeights pv;
+    GraphNetWeights gn;
+    DqnWeights dqn;
+    void *weight_blob;    // single allocation backing all weights
+    double *log_table;    // device
+    double *tanh_table;   // device
+    int32_t n_log, n_tanh;
+    TreeArrays tree;
+    SimArrays sim;
+    // network activations (fp32 path): three ping-pong buffers [G][128][225]
+    float *act[3];
+    float *gn_logits, *gn_policy, *dqn_q;   // [G][225] each
+    float *pv_logits, *pv_probs, *pv_value; // [G][225], [G][225], [G]
+    gz_board *tmp_boards; // [G]
+    uint8_t *tmp_u8;      // [G*232] host-call staging: cells, to_move, ai_player, move_count
+    int32_t *io_cv;       // [G][225] host-call result staging
+    double *io_cval;      // [G][225]
+    int32_t *io_best;     // [G]
+    unsigned long long *counters; // device gz_counters-shaped
+    int64_t launches;     // host-side launch counter
+    bool searched;
+};
+
+struct SearchCfg {
+    int32_t S;
+    int32_t planner_steps, planner_k, deterministic, eval_nodes;
+    double c_puct, beta, alpha, explore;
+    uint32_t seed_lo, seed_hi, game_base;
+};
+
+// ---- launchers -------------------------------------------------------------------------------
+// board kernels (gz_kernels_board.cu)
+void launch_boards_from_cells(const uint8_t *cells, const uint8_t *to_move, const uint16_t *mc, int G,
+                              gz_board *out, cudaStream_t s);
+void launch_boards_to_cells(const gz_board *b, int G, uint8_t *cells, cudaStream_t s);
+void launch_make_moves(gz_board *b, const int32_t *moves, int G, uint8_t *ok, cudaStream_t s);
+void launch_board_ops(const gz_board *b, int G, uint32_t *legal, uint32_t *win, uint32_t *three,
+                      int32_t *threat, int64_t *pattern, cudaStream_t s);
+
+// rollout kernels (gz_kernels_rollout.cu)
+void launch_rollout_policy(const gz_board *b, int G, const SearchCfg &c, int sim, int step,
+                           int32_t *move, uint32_t *cand, cudaStream_t s);
+void launch_rollout_tail(gz_board *b, const uint8_t *ai_player, int32_t *steps, int G,
+                         const SearchCfg &c, int sim, double *value, unsigned long long *counters,
+                         cudaStream_t s);
+
+// planner kernels (gz_kernels_planner.cu)
+void launch_planner_score(const gz_board *b, const uint8_t *ai_player, const int32_t *steps, int G,
+                          const SearchCfg &c, int planner_step, int32_t *topk, int32_t *ntop,
+                          int64_t *scores2, cudaStream_t s);
+void launch_planner_pick(gz_board *b, const uint8_t *ai_player, int32_t *steps, int G,
+                         const SearchCfg &c, int sim, int planner_step, const int32_t *topk,
+                         const int32_t *ntop, const float *gn_policy, const float *dqn_q,
+                         double *composed, int32_t *move_out, bool apply_move,
+                         unsigned long long *counters, cudaStream_t s);
+
+// tree kernels (gz_kernels_tree.cu)
+void launch_tree_init(const Engine &e, const gz_board *boards, const uint8_t *ai_player, int G,
+                      cudaStream_t s);
+void launch_tree_step(const Engine &e, int G, const SearchCfg &c, int sim, cudaStream_t s);
+void launch_tree_finalize(const Engine &e, int G, const SearchCfg &c, int32_t *child_visits,
+                          double *child_value, int32_t *best_move, cudaStream_t s);
+
+// networks, fp32 path (gz_nn_fp32.cu)
+void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active, int G,
+                        float *logits, float *probs, float *value, float *prior_out,
+                        const int32_t *prior_slot, cudaStream_t s);
+void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn_logits,
+                             float *gn_policy, float *dqn_q, cudaStream_t s);
+
+}  // namespace gz

@@ -1,0 +1,134 @@
+// gz_kernels_planner.cu -- BGPlannerAI.get_move without the networks (bg_planner.py:232-269):
+//   k_planner_score: KnowledgeSearch.top_k_moves -- score every empty cell, stable descending top-k
+//                    (one warp per board, lane = bit position inside each bitboard word)
+//   k_planner_pick : blend GraphNet's softmax with the DQN output over the k candidates, explore
+//                    roll, optional make_move (one thread per board)
+// Integer-ALU bound; per board-step 80 B in, <= 72 B out.
+#include "gz_engine.h"
+#include "gz_warp.cuh"
+
+namespace gz {
+
+constexpr long long kNoScore = INT64_MIN;
+
+__global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restrict__ boards,
+                                                       const uint8_t *__restrict__ ai_player, int G,
+                                                       int k, int32_t *__restrict__ topk,
+                                                       int32_t *__restrict__ ntop,
+                                                       int64_t *__restrict__ scores2) {
+    int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (g >= G) return;
+    gz_board b = boards[g];
+    if (b.status != 0) {  // _simulate's planner loop stops at game_over (ai_agent.py:266)
+        if (lane == 0) ntop[g] = 0;
+        if (lane < kMaxTopK) topk[g * kMaxTopK + lane] = -1;
+        if (scores2)
+            for (int i = lane; i < kCells; i += 32) scores2[(size_t)g * kCells + i] = kNoScore;
+        return;
+    }
+    BB black = bb_load(b.stones[0]), white = bb_load(b.stones[1]);
+    BB empty = bb_empty_cells(black, white);
+    int a = ai_player[g];
+    const BB a_st = (a == 1) ? black : white;
+    const BB o_st = (a == 1) ? white : black;
+    long long s_a = warp_pattern_score(a_st, empty, lane);
+    BB win_b, three_b;
+    win_three_masks(o_st, empty, win_b, three_b);
+    long long sc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        int p = 32 * i + lane;
+        sc[i] = ((empty.w[i] >> lane) & 1u) ? planner_score2(b, black, white, empty, a, s_a, win_b, p)
+                                            : kNoScore;
+        if (scores2 && (p >> 4) < 15 && (p & 15) < 15) scores2[(size_t)g * kCells + bit_to_cell(p)] = sc[i];
+    }
+    // stable descending top-k: k rounds of (max score, smallest position)
+    int n = 0;
+    for (int j = 0; j < k; ++j) {
+        long long best = kNoScore;
+        int bi = -1;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            if (sc[i] != kNoScore && (bi < 0 || sc[i] > best)) { best = sc[i]; bi = 32 * i + lane; }
+        warp_argmax_first_ll(best, bi);
+        if (bi < 0) break;
+        if ((bi & 31) == lane) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i == (bi >> 5)) sc[i] = kNoScore;
+        }
+        if (lane == 0) topk[g * kMaxTopK + j] = bit_to_cell(bi);
+        ++n;
+    }
+    if (lane == 0) {
+        ntop[g] = n;
+        for (int j = n; j < kMaxTopK; ++j) topk[g * kMaxTopK + j] = -1;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boards,
+                                                      int32_t *__restrict__ steps, int G, SearchCfg c,
+                                                      int sim, int step_override,
+                                                      const int32_t *__restrict__ topk,
+                                                      const int32_t *__restrict__ ntop,
+                                                      const float *__restrict__ policy,
+                                                      const float *__restrict__ q,
+                                                      double *__restrict__ composed,
+                                                      int32_t *__restrict__ move_out, int apply_move,
+                                                      unsigned long long *__restrict__ counters) {
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    int did = 0;
+    if (g < G) {
+        int n = ntop[g];
+        int mv = -1;
+        if (n > 0) {
+            int step = step_override >= 0 ? step_override : steps[g];
+            double best_score = -1e18;
+            int best = -1;
+            double a = c.alpha, na = 1.0 - c.alpha;
+            for (int j = 0; j < n; ++j) {
+                int idx = topk[g * kMaxTopK + j];
+                double comp = __dsub_rn(__dmul_rn(a, (double)policy[(size_t)g * kCells + idx]),
+                                        __dmul_rn(na, (double)q[(size_t)g * kCells + idx]));
+                if (composed) composed[g * kMaxTopK + j] = comp;
+                if (comp > best_score) { best_score = comp; best = idx; }   // strict: first maximum
+            }
+            RolloutRng rng = {c.seed_lo, c.seed_hi, c.game_base + (uint32_t)g, (uint32_t)sim, c.deterministic != 0};
+            // random.random() is always drawn (bg_planner.py:267)
+            if (rng_random(rng, step) < c.explore) mv = topk[g * kMaxTopK + rng_choice(rng, step, n)];
+            else mv = best >= 0 ? best : topk[g * kMaxTopK];
+            if (apply_move) {
+                gz_board b = boards[g];
+                board_place(b, cell_to_bit(mv));
+                boards[g] = b;
+                steps[g] = steps[g] + 1;
+                did = 1;
+            }
+        }
+        if (composed) for (int j = (n > 0 ? n : 0); j < kMaxTopK; ++j) composed[g * kMaxTopK + j] = 0.0;
+        if (move_out) move_out[g] = mv;
+    }
+    for (int o = 16; o > 0; o >>= 1) did += __shfl_xor_sync(0xffffffffu, did, o);
+    if (counters && (threadIdx.x & 31) == 0 && did) atomicAdd(&counters[3], (unsigned long long)did);
+}
+
+void launch_planner_score(const gz_board *b, const uint8_t *ai_player, const int32_t *steps, int G,
+                          const SearchCfg &c, int planner_step, int32_t *topk, int32_t *ntop,
+                          int64_t *scores2, cudaStream_t s) {
+    (void)steps; (void)planner_step;
+    int k = c.planner_k < kMaxTopK ? c.planner_k : kMaxTopK;
+    k_planner_score<<<(G * 32 + 127) / 128, 128, 0, s>>>(b, ai_player, G, k, topk, ntop, scores2);
+}
+void launch_planner_pick(gz_board *b, const uint8_t *ai_player, int32_t *steps, int G,
+                         const SearchCfg &c, int sim, int planner_step, const int32_t *topk,
+                         const int32_t *ntop, const float *gn_policy, const float *dqn_q,
+                         double *composed, int32_t *move_out, bool apply_move,
+                         unsigned long long *counters, cudaStream_t s) {
+    (void)ai_player;
+    k_planner_pick<<<(G + 127) / 128, 128, 0, s>>>(b, steps, G, c, sim, planner_step, topk, ntop,
+                                                   gn_policy, dqn_q, composed, move_out,
+                                                   apply_move ? 1 : 0, counters);
+}
+
+}  // namespace gz

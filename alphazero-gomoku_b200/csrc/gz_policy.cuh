@@ -145,7 +145,6 @@ constexpr int64_t kScoreLose2 = -200000;
 GZ_HD int64_t planner_score2(const gz_board &b, const BB &black, const BB &white, const BB &empty,
                              int a, int64_t s_a, const BB &win_b, int p) {
     int mover = b.to_move;
-    int other = 3 - a;
     const BB &a_st = (a == 1) ? black : white;
     const BB &o_st = (a == 1) ? white : black;
     BB mv = (mover == 1) ? black : white;
@@ -179,7 +178,6 @@ GZ_HD int64_t planner_score2(const gz_board &b, const BB &black, const BB &white
     int dist = (r < 7 ? 7 - r : r - 7) + (c < 7 ? 7 - c : c - 7);
     int bias2 = 6 - dist;
     if (bias2 < 0) bias2 = 0;
-    (void)other;
     return 2 * (s_a + d) + bias2;
 }
 

@@ -1,0 +1,289 @@
+"""ctypes binding of libgomoku_b200.so (include/gomoku_b200.h) plus a thin torch-tensor wrapper.
+
+PyTorch is plumbing here: it owns device memory and streams; every computation on the hot path is
+a kernel inside libgomoku_b200.so.  There is no CPU fallback: constructing an Engine without a
+CUDA device, or without the built library, raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libgomoku_b200.so")
+_LIB = None
+
+PLANNER_PRESETS = {"easy": (8, 0.5, 0.2), "medium": (12, 0.65, 0.1), "hard": (16, 0.75, 0.05)}
+
+EXPORTS = [
+    "gz_create", "gz_destroy", "gz_last_error", "gz_version", "gz_set_pv_weights",
+    "gz_set_planner_weights", "gz_set_tables", "gz_pv_param_count", "gz_graphnet_param_count",
+    "gz_dqn_param_count", "gz_boards_from_cells", "gz_boards_to_cells", "gz_make_moves",
+    "gz_board_ops", "gz_pv_forward", "gz_planner_nets_forward", "gz_planner_move",
+    "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
+    "gz_get_counters", "gz_reset_counters",
+]
+
+
+class GzConfig(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_games", C.c_int32), ("max_simulations", C.c_int32),
+                ("precision", C.c_int32), ("store_priors", C.c_int32)]
+
+
+class GzSearchParams(C.Structure):
+    _fields_ = [("num_simulations", C.c_int32), ("planner_steps", C.c_int32),
+                ("planner_k", C.c_int32), ("deterministic", C.c_int32), ("c_puct", C.c_double),
+                ("beta", C.c_double), ("planner_alpha", C.c_double), ("planner_explore", C.c_double),
+                ("seed", C.c_uint64), ("game_base", C.c_uint32), ("eval_nodes", C.c_int32)]
+
+
+class GzCounters(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("simulations", "nodes_created", "pv_evals", "planner_steps",
+                                          "rollout_steps", "terminal_leaves", "kernel_launches")]
+
+
+BOARD_BYTES = 80
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def load_library(path=None):
+    """dlopen the engine.  Raises if it was not built: the product never runs without it."""
+    global _LIB
+    if _LIB is None:
+        path = path or _SO
+        if not os.path.exists(path):
+            raise EngineError("libgomoku_b200.so is missing (%s): run `python alphazero-gomoku_b200/"
+                              "build.py`; there is no fallback path" % path)
+        L = C.CDLL(path)
+        L.gz_last_error.restype = C.c_char_p
+        for f in ("gz_pv_param_count", "gz_graphnet_param_count", "gz_dqn_param_count"):
+            getattr(L, f).restype = C.c_int64
+        _LIB = L
+    return _LIB
+
+
+def flatten_state_dict(sd):
+    """torch/numpy state dict -> one float32 vector in state-dict order without BN counters."""
+    parts = []
+    for k, v in sd.items():
+        if k.endswith("num_batches_tracked"):
+            continue
+        a = v.detach().cpu().numpy() if hasattr(v, "detach") else np.asarray(v)
+        parts.append(np.asarray(a, dtype=np.float32).reshape(-1))
+    return np.ascontiguousarray(np.concatenate(parts))
+
+
+def make_params(sims, c_puct, beta=0.2, planner_steps=0, difficulty="medium", deterministic=False,
+                seed=0, game_base=0, eval_nodes=True):
+    k, a, e = PLANNER_PRESETS.get(difficulty, PLANNER_PRESETS["medium"])
+    return GzSearchParams(int(sims), int(max(0, planner_steps)), k, int(bool(deterministic)),
+                          float(c_puct), float(beta), a, e, int(seed) & (2 ** 64 - 1),
+                          int(game_base), int(bool(eval_nodes)))
+
+
+def _ptr(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+class Engine:
+    """One engine handle on one GPU; all tensors it returns live on that GPU."""
+
+    def __init__(self, max_games, max_simulations, device=0, precision=0, store_priors=False,
+                 host_tables=True):
+        import torch
+        self.torch = torch
+        self.L = load_library()
+        if not torch.cuda.is_available():
+            raise EngineError("no CUDA device: the B200 engine has no CPU path")
+        self.device = torch.device("cuda", device)
+        self.max_games, self.max_simulations = int(max_games), int(max_simulations)
+        cfg = GzConfig(device, self.max_games, self.max_simulations, precision, int(store_priors))
+        self.h = C.c_void_p()
+        self._ck(self.L.gz_create(C.byref(cfg), C.byref(self.h)))
+        if host_tables:
+            n = min(2048, self.max_simulations + 2)
+            logt = np.zeros(n, np.float64)
+            logt[1:] = [float(np.log(i)) for i in range(1, n)]
+            tanht = np.array([float(np.tanh((i * 50.0) / 10000.0)) for i in range(4096)], np.float64)
+            self._ck(self.L.gz_set_tables(self.h, logt.ctypes.data_as(C.c_void_p), n,
+                                          tanht.ctypes.data_as(C.c_void_p), 4096))
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.L.gz_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise EngineError("gomoku_b200 error %d: %s" % (rc, self.L.gz_last_error().decode()))
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ---- weights
+    def set_pv_weights(self, state_dict):
+        f = flatten_state_dict(state_dict)
+        self._ck(self.L.gz_set_pv_weights(self.h, f.ctypes.data_as(C.c_void_p), C.c_int64(f.size)))
+
+    def set_planner_weights(self, graphnet_sd, dqn_sd):
+        g, d = flatten_state_dict(graphnet_sd), flatten_state_dict(dqn_sd)
+        self._ck(self.L.gz_set_planner_weights(self.h, g.ctypes.data_as(C.c_void_p), C.c_int64(g.size),
+                                               d.ctypes.data_as(C.c_void_p), C.c_int64(d.size)))
+
+    # ---- boards
+    def boards_from_cells(self, cells, to_move, move_count):
+        t = self.torch
+        cells = t.as_tensor(np.ascontiguousarray(cells, np.uint8)).to(self.device).reshape(-1, 225)
+        G = cells.shape[0]
+        tm = t.as_tensor(np.ascontiguousarray(to_move, np.uint8)).to(self.device)
+        mc = t.as_tensor(np.ascontiguousarray(move_count, np.int16)).to(self.device)
+        boards = t.empty((G, BOARD_BYTES), dtype=t.uint8, device=self.device)
+        self._ck(self.L.gz_boards_from_cells(self.h, _ptr(cells), _ptr(tm), _ptr(mc), G, _ptr(boards),
+                                             self._stream()))
+        return boards
+
+    def boards_to_cells(self, boards):
+        G = boards.shape[0]
+        out = self.torch.empty((G, 225), dtype=self.torch.uint8, device=self.device)
+        self._ck(self.L.gz_boards_to_cells(self.h, _ptr(boards), G, _ptr(out), self._stream()))
+        return out
+
+    def board_meta(self, boards):
+        """(move_count, to_move, status) numpy arrays decoded from the 80-byte records."""
+        raw = boards.cpu().numpy()
+        mc = raw[:, 64:66].copy().view(np.uint16).reshape(-1)
+        return mc, raw[:, 66].copy(), raw[:, 67].copy()
+
+    def make_moves(self, boards, moves):
+        t = self.torch
+        G = boards.shape[0]
+        mv = t.as_tensor(np.ascontiguousarray(moves, np.int32)).to(self.device)
+        ok = t.empty(G, dtype=t.uint8, device=self.device)
+        self._ck(self.L.gz_make_moves(self.h, _ptr(boards), _ptr(mv), G, _ptr(ok), self._stream()))
+        return ok
+
+    def board_ops(self, boards):
+        t = self.torch
+        G = boards.shape[0]
+        legal = t.empty((G, 8), dtype=t.int32, device=self.device)
+        win = t.empty((G, 2, 8), dtype=t.int32, device=self.device)
+        three = t.empty((G, 2, 8), dtype=t.int32, device=self.device)
+        threat = t.empty((G, 2), dtype=t.int32, device=self.device)
+        pattern = t.empty((G, 2), dtype=t.int64, device=self.device)
+        self._ck(self.L.gz_board_ops(self.h, _ptr(boards), G, _ptr(legal), _ptr(win), _ptr(three),
+                                     _ptr(threat), _ptr(pattern), self._stream()))
+        return dict(legal=legal, win=win, three=three, threat=threat, pattern=pattern)
+
+    # ---- networks
+    def pv_forward(self, boards):
+        t = self.torch
+        G = boards.shape[0]
+        logits = t.empty((G, 225), dtype=t.float32, device=self.device)
+        probs = t.empty_like(logits)
+        value = t.empty(G, dtype=t.float32, device=self.device)
+        self._ck(self.L.gz_pv_forward(self.h, _ptr(boards), G, _ptr(logits), _ptr(probs), _ptr(value),
+                                      self._stream()))
+        return logits, probs, value
+
+    def planner_nets_forward(self, boards):
+        t = self.torch
+        G = boards.shape[0]
+        lg = t.empty((G, 225), dtype=t.float32, device=self.device)
+        pol = t.empty_like(lg)
+        q = t.empty_like(lg)
+        self._ck(self.L.gz_planner_nets_forward(self.h, _ptr(boards), G, _ptr(lg), _ptr(pol), _ptr(q),
+                                                self._stream()))
+        return lg, pol, q
+
+    # ---- planner / rollout
+    def _ai(self, ai_player, G):
+        a = np.broadcast_to(np.asarray(ai_player, np.uint8), (G,))
+        return self.torch.as_tensor(np.ascontiguousarray(a)).to(self.device)
+
+    def planner_move(self, boards, ai_player, params, sim=0, step=0):
+        t = self.torch
+        G = boards.shape[0]
+        ai = self._ai(ai_player, G)
+        scores2 = t.empty((G, 225), dtype=t.int64, device=self.device)
+        topk = t.empty((G, 16), dtype=t.int32, device=self.device)
+        comp = t.empty((G, 16), dtype=t.float64, device=self.device)
+        move = t.empty(G, dtype=t.int32, device=self.device)
+        self._ck(self.L.gz_planner_move(self.h, _ptr(boards), _ptr(ai), G, C.byref(params), sim, step,
+                                        _ptr(scores2), _ptr(topk), _ptr(comp), _ptr(move),
+                                        self._stream()))
+        return dict(scores2=scores2, topk=topk, composed=comp, move=move)
+
+    def rollout_policy(self, boards, params, sim=0, step=0):
+        t = self.torch
+        G = boards.shape[0]
+        move = t.empty(G, dtype=t.int32, device=self.device)
+        cand = t.empty((G, 8), dtype=t.int32, device=self.device)
+        self._ck(self.L.gz_rollout_policy(self.h, _ptr(boards), G, C.byref(params), sim, step,
+                                          _ptr(move), _ptr(cand), self._stream()))
+        return move, cand
+
+    def rollout(self, boards, ai_player, params, sim=0):
+        t = self.torch
+        G = boards.shape[0]
+        ai = self._ai(ai_player, G)
+        value = t.empty(G, dtype=t.float64, device=self.device)
+        steps = t.empty(G, dtype=t.int32, device=self.device)
+        final = t.empty((G, BOARD_BYTES), dtype=t.uint8, device=self.device)
+        self._ck(self.L.gz_rollout(self.h, _ptr(boards), _ptr(ai), G, C.byref(params), sim,
+                                   _ptr(value), _ptr(steps), _ptr(final), self._stream()))
+        return value, steps, final
+
+    # ---- search
+    def search(self, boards, ai_player, params):
+        t = self.torch
+        G = boards.shape[0]
+        ai = self._ai(ai_player, G)
+        cv = t.empty((G, 225), dtype=t.int32, device=self.device)
+        cval = t.empty((G, 225), dtype=t.float64, device=self.device)
+        best = t.empty(G, dtype=t.int32, device=self.device)
+        self._ck(self.L.gz_search(self.h, _ptr(boards), _ptr(ai), G, C.byref(params), _ptr(cv),
+                                  _ptr(cval), _ptr(best), self._stream()))
+        return cv, cval, best
+
+    def search_host(self, cells, to_move, move_count, ai_player, params, out=None):
+        """Host buffers in, host buffers out (the call behind get_move)."""
+        cells = np.ascontiguousarray(cells, np.uint8).reshape(-1, 225)
+        G = cells.shape[0]
+        tm = np.ascontiguousarray(np.broadcast_to(np.asarray(to_move, np.uint8), (G,)))
+        mc = np.ascontiguousarray(np.broadcast_to(np.asarray(move_count, np.uint16), (G,)))
+        ai = np.ascontiguousarray(np.broadcast_to(np.asarray(ai_player, np.uint8), (G,)))
+        if out is None:
+            out = (np.empty((G, 225), np.int32), np.empty((G, 225), np.float64), np.empty(G, np.int32))
+        cv, cval, best = out
+        P = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        self._ck(self.L.gz_search_host(self.h, P(cells), P(tm), P(mc), P(ai), G, C.byref(params),
+                                       P(cv), P(cval), P(best)))
+        return cv, cval, best
+
+    def get_tree(self, g):
+        cap = self.max_simulations + 1
+        parent = np.empty(cap, np.int32); move = np.empty(cap, np.int32)
+        visits = np.empty(cap, np.int32); value = np.empty(cap, np.float64)
+        n = C.c_int32()
+        P = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        self._ck(self.L.gz_get_tree(self.h, int(g), cap, P(parent), P(move), P(visits), P(value),
+                                    C.byref(n)))
+        k = n.value
+        return dict(parent=parent[:k], move=move[:k], visits=visits[:k], value=value[:k])
+
+    def counters(self):
+        c = GzCounters()
+        self._ck(self.L.gz_get_counters(self.h, C.byref(c)))
+        return {n: getattr(c, n) for n, _ in GzCounters._fields_}
+
+    def reset_counters(self):
+        self._ck(self.L.gz_reset_counters(self.h))
