@@ -58,8 +58,7 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
         return fail(GZ_ERR_CUDA, "gz_create: no CUDA device (%s); this library has no CPU path",
                     cudaGetErrorString(e0));
     CK(cudaSetDevice(cfg->device));
-    Engine *e = new Engine();
-    memset(e, 0, sizeof *e);
+    Engine *e = new Engine();   // value-initialised: every POD member is zero
     e->cfg = *cfg;
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, cfg->device));
@@ -105,6 +104,7 @@ extern "C" int gz_destroy(gz_handle h) {
                     e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
                     e->tanh_table, e->weight_blob, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
+    for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
     cudaStreamDestroy(e->own_stream);
     delete e;
     return GZ_OK;
@@ -406,16 +406,20 @@ extern "C" int gz_rollout_policy(gz_handle h, const gz_board *d_boards, int32_t 
 // planner prefix + tail on e->sim.board / e->sim.steps (already initialised by the caller)
 static void run_playouts(Engine *e, int G, const SearchCfg &c, int sim, cudaStream_t s) {
     for (int k = 0; k < c.planner_steps; ++k) {
+        prof_begin(*e, GZ_STAGE_PLAN_SCORE, 1, s);
         launch_planner_score(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, k, e->sim.topk,
                              e->sim.ntop, nullptr, s);
+        prof_end(*e, s);
         nn_planner_forward_fp32(*e, e->sim.board, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+        prof_begin(*e, GZ_STAGE_PLAN_PICK, 1, s);
         launch_planner_pick(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, sim, -1, e->sim.topk,
                             e->sim.ntop, e->gn_policy, e->dqn_q, nullptr, nullptr, true, e->counters, s);
-        e->launches += 2;
+        prof_end(*e, s);
     }
+    prof_begin(*e, GZ_STAGE_ROLLOUT, 1, s);
     launch_rollout_tail(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, sim, e->sim.value,
                         e->counters, s);
-    e->launches += 1;
+    prof_end(*e, s);
 }
 
 extern "C" int gz_rollout(gz_handle h, const gz_board *d_boards, const uint8_t *d_ai_player, int32_t G,
@@ -447,22 +451,25 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     if (c.S < 1 || c.S > e->cfg.max_simulations) return fail(GZ_ERR_ARG, "gz_search: num_simulations out of range");
     if (c.eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_search: gz_set_pv_weights was not called");
     if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_search: planner weights not set");
+    prof_begin(*e, GZ_STAGE_TREE, 1, s);
     launch_tree_init(*e, d_boards, d_ai, G, s);
-    e->launches += 1;
+    prof_end(*e, s);
     if (c.eval_nodes)
         nn_pv_forward_fp32(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
                            e->tree.prior, e->sim.leaf, s);
     for (int sim = 0; sim < c.S; ++sim) {
+        prof_begin(*e, GZ_STAGE_TREE, 1, s);
         launch_tree_step(*e, G, c, sim, s);
-        e->launches += 1;
+        prof_end(*e, s);
         if (c.eval_nodes)
             nn_pv_forward_fp32(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
                                e->tree.prior, e->sim.leaf, s);
         run_playouts(e, G, c, sim, s);
     }
+    prof_begin(*e, GZ_STAGE_TREE, 2, s);
     launch_tree_step(*e, G, c, c.S, s);   // backs up the last simulation
     launch_tree_finalize(*e, G, c, d_cv, d_cval, d_best, s);
-    e->launches += 2;
+    prof_end(*e, s);
     CKL();
     e->searched = true;
     return GZ_OK;
@@ -558,5 +565,56 @@ extern "C" int gz_reset_counters(gz_handle h) {
     CK(cudaDeviceSynchronize());
     CK(cudaMemset(e->counters, 0, 8 * sizeof(unsigned long long)));
     e->launches = 0;
+    return GZ_OK;
+}
+
+// ---- stage timing --------------------------------------------------------------------------------
+namespace gz {
+static cudaEvent_t next_event(Engine &e) {
+    if (e.ev_used == e.ev_pool.size()) {
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        e.ev_pool.push_back(ev);
+    }
+    return e.ev_pool[e.ev_used++];
+}
+void prof_begin(Engine &e, int stage, int n_launches, cudaStream_t s) {
+    e.launches += n_launches;
+    if (!e.profiling) return;
+    e.ev_stage.push_back(stage);
+    e.stage_launches[stage] += n_launches;
+    cudaEventRecord(next_event(e), s);
+}
+void prof_end(Engine &e, cudaStream_t s) {
+    if (!e.profiling) return;
+    cudaEventRecord(next_event(e), s);
+}
+}  // namespace gz
+
+extern "C" int gz_set_profiling(gz_handle h, int32_t on) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_set_profiling: null handle");
+    e->profiling = on != 0;
+    return GZ_OK;
+}
+
+extern "C" int gz_get_stage_times(gz_handle h, double *h_ms, int64_t *h_launches) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_get_stage_times: null handle");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    for (size_t i = 0; i + 1 < e->ev_used && i / 2 < e->ev_stage.size(); i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e->ev_pool[i], e->ev_pool[i + 1]));
+        e->stage_ms[e->ev_stage[i / 2]] += ms;
+    }
+    e->ev_used = 0;
+    e->ev_stage.clear();
+    for (int i = 0; i < GZ_N_STAGES; ++i) {
+        if (h_ms) h_ms[i] = e->stage_ms[i];
+        if (h_launches) h_launches[i] = e->stage_launches[i];
+        e->stage_ms[i] = 0.0;
+        e->stage_launches[i] = 0;
+    }
     return GZ_OK;
 }

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <vector>
+
 #include "../../include/gomoku_b200.h"
 
 namespace gz {
@@ -97,7 +99,18 @@ struct Engine {
     unsigned long long *counters; // device gz_counters-shaped
     int64_t launches;     // host-side launch counter
     bool searched;
+    // optional stage timing with CUDA events on the launching stream (gz_set_profiling)
+    bool profiling;
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<int> ev_stage;      // stage id of the interval starting at event 2*i
+    size_t ev_used;
+    double stage_ms[GZ_N_STAGES];
+    int64_t stage_launches[GZ_N_STAGES];
 };
+
+// brackets `n_launches` kernel launches of stage `stage` with events when profiling is on
+void prof_begin(Engine &e, int stage, int n_launches, cudaStream_t s);
+void prof_end(Engine &e, cudaStream_t s);
 
 struct SearchCfg {
     int32_t S;

@@ -286,16 +286,21 @@ void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active
                         const int32_t *prior_slot, cudaStream_t s) {
     const PvWeights &w = e.pv;
     float *a0 = e.act[0], *a1 = e.act[1], *a2 = e.act[2];
+    prof_begin(e, GZ_STAGE_PV_CONV0, 1, s);
     k_conv<3, 128, 3, true, false, true><<<G, 256, 0, s>>>(nullptr, boards, active, w.conv0.w, w.conv0.b, nullptr, a0);
+    prof_end(e, s);
+    prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
     k_conv<128, 128, 3, false, false, true><<<G, 256, 0, s>>>(a0, nullptr, active, w.tower[0].w, w.tower[0].b, nullptr, a1);
     k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, active, w.tower[1].w, w.tower[1].b, a0, a2);
     k_conv<128, 128, 3, false, false, true><<<G, 256, 0, s>>>(a2, nullptr, active, w.tower[2].w, w.tower[2].b, nullptr, a1);
     k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, active, w.tower[3].w, w.tower[3].b, a2, a0);
+    prof_end(e, s);
+    prof_begin(e, GZ_STAGE_PV_HEADS, 1, s);
     k_heads<128, true><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
         a0, boards, active, G, w.pconv_w, w.pconv_b, w.pfc_wt, w.pfc_b, w.vconv_w, w.vconv_b,
         w.vfc1_wt, w.vfc1_b, w.vfc2_w, w.vfc2_b, logits, probs, value, prior_out, prior_slot,
         e.tree.cap, prior_slot ? e.tree.vhead : nullptr);
-    e.launches += 6;
+    prof_end(e, s);
 }
 
 void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn_logits,
@@ -303,16 +308,21 @@ void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn
     const GraphNetWeights &w = e.gn;
     float *a0 = e.act[0], *a1 = e.act[1];
     // the planner nets only see live rollout boards; finished ones are skipped via status
+    prof_begin(e, GZ_STAGE_GN_CONVS, 9, s);
     k_conv<3, 64, 3, true, false, true><<<G, 128, 0, s>>>(nullptr, boards, nullptr, w.embed.w, w.embed.b, nullptr, a0);
     for (int i = 0; i < 4; ++i) {
         k_conv<64, 64, 3, false, false, true><<<G, 128, 0, s>>>(a0, nullptr, nullptr, w.l3[i].w, w.l3[i].b, nullptr, a1);
         k_conv<64, 64, 1, false, false, true><<<G, 128, 0, s>>>(a1, nullptr, nullptr, w.l1[i].w, w.l1[i].b, nullptr, a0);
     }
+    prof_end(e, s);
+    prof_begin(e, GZ_STAGE_GN_HEAD, 1, s);
     k_heads<64, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
         a0, boards, nullptr, G, w.hconv_w, w.hconv_b, w.hfc_wt, w.hfc_b, nullptr, nullptr, nullptr,
         nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr, nullptr, nullptr, 0, nullptr);
+    prof_end(e, s);
+    prof_begin(e, GZ_STAGE_DQN, 1, s);
     k_dqn<<<(G + kDqnNB - 1) / kDqnNB, 256, 0, s>>>(boards, nullptr, G, e.dqn, dqn_q);
-    e.launches += 11;
+    prof_end(e, s);
 }
 
 }  // namespace gz

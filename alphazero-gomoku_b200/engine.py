@@ -21,8 +21,11 @@ EXPORTS = [
     "gz_dqn_param_count", "gz_boards_from_cells", "gz_boards_to_cells", "gz_make_moves",
     "gz_board_ops", "gz_pv_forward", "gz_planner_nets_forward", "gz_planner_move",
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
-    "gz_get_counters", "gz_reset_counters",
+    "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_get_stage_times",
 ]
+
+STAGES = ["tree", "pv_conv0", "pv_tower", "pv_heads", "planner_score", "gn_convs", "gn_head", "dqn",
+          "planner_pick", "rollout_tail", "misc", "reserved"]
 
 
 class GzConfig(C.Structure):
@@ -284,6 +287,16 @@ class Engine:
         c = GzCounters()
         self._ck(self.L.gz_get_counters(self.h, C.byref(c)))
         return {n: getattr(c, n) for n, _ in GzCounters._fields_}
+
+    def set_profiling(self, on):
+        self._ck(self.L.gz_set_profiling(self.h, int(bool(on))))
+
+    def stage_times(self):
+        """{stage: (milliseconds, launches)} accumulated since the last call (CUDA events)."""
+        ms = (C.c_double * len(STAGES))()
+        ln = (C.c_int64 * len(STAGES))()
+        self._ck(self.L.gz_get_stage_times(self.h, ms, ln))
+        return {n: (ms[i], ln[i]) for i, n in enumerate(STAGES)}
 
     def reset_counters(self):
         self._ck(self.L.gz_reset_counters(self.h))

@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""Benchmark of the MCTS hot path (BASELINE.json metric: MCTS simulations/s, 15x15, "hard").
+
+    python bench.py --gpus N --steps K --warmup W            # the B200 engine
+    python bench.py --impl reference --steps K --warmup W    # the CPU baseline arm (oracle port)
+
+A step = one search pass (gz_search) over one batch of G synthetic positions: S simulations per
+position, each simulation = select + expand + policy-value forward of the new node + planner-guided
+playout + backup.  Workload at N=1 = BASELINE config 3: hard preset, S=200,
+c_puct=1.8, beta=0.2, planner_steps=5, G=4096 concurrent games.  With N>1 every rank runs its own
+G games (weak scaling, no collective on the hot path; game ids are global so per-game random
+streams do not depend on N).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "alphazero-gomoku_b200"))
+
+# algorithmic FLOPs (2 x MACs) per unit, from the layer shapes
+F_PV_CONV0 = 2 * 27 * 128 * 225
+F_PV_TOWER = 4 * 2 * 1152 * 128 * 225                  # four 128->128 3x3 convolutions
+F_PV_HEADS = 2 * (128 * 3 * 225 + 450 * 225 + 225 * 64 + 64)
+F_GN_CONVS = 2 * 27 * 64 * 225 + 4 * (2 * 576 * 64 * 225 + 2 * 64 * 64 * 225)
+F_GN_HEAD = 2 * (64 * 2 * 225 + 450 * 225)
+F_DQN = 2 * (675 * 256 + 256 * 256 + 256 * 225)
+STAGE_FLOPS = {"pv_conv0": ("pv_evals", F_PV_CONV0), "pv_tower": ("pv_evals", F_PV_TOWER),
+               "pv_heads": ("pv_evals", F_PV_HEADS), "gn_convs": ("planner_steps", F_GN_CONVS),
+               "gn_head": ("planner_steps", F_GN_HEAD), "dqn": ("planner_steps", F_DQN)}
+# algorithmic HBM bytes per unit for the integer kernels (board in + result out)
+STAGE_BYTES = {"tree": ("simulations", 80 + 100 + 48), "planner_score": ("planner_steps", 80 + 68),
+               "planner_pick": ("planner_steps", 80 + 80 + 16 * 8 + 68), "rollout_tail": ("simulations", 80 + 80 + 12)}
+
+PRESET = dict(sims=200, c_puct=1.8, beta=0.2, planner_steps=5, difficulty="hard")
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=float(p["hbm_gbs"]), tf_burst=float(p["bf16_tflops"]),
+                    tf_sustained=float(p["bf16_tflops_sustained"]), source="measured")
+    except Exception:
+        return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks and throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4)
+                          if len(r) > 2 + i and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def synthetic_weights():
+    """Random-init weights of the three architectures (torch default init, seed 1234)."""
+    import torch
+    import bg_planner
+    import neural_network
+    torch.manual_seed(1234)
+    pv = neural_network.AlphaZeroGomokuNet()
+    gn, dq = bg_planner.GraphNet(), bg_planner.OpponentDQN()
+    return pv.state_dict(), gn.state_dict(), dq.state_dict()
+
+
+# ---------------------------------------------------------------------------------------- CPU arm
+def cpu_sample(cells, to_move, count, seconds, sims_per_search, threads=None, fixed_searches=None):
+    """Times the oracle port (oracle/gomoku_oracle.c: the reference's algorithm restated in C, pinned
+    to the Python reference's goldens) on the host cores: every thread runs whole searches of
+    `sims_per_search` simulations with the workload's preset on its share of the positions."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as orc
+    pv, gn, dq = synthetic_weights()
+    O = orc.Oracle(pv={k: v.numpy() for k, v in pv.items()}, graphnet={k: v.numpy() for k, v in gn.items()},
+                   dqn={k: v.numpy() for k, v in dq.items()})
+    threads = threads or os.cpu_count() or 1
+    done = [0] * threads
+    deadline = time.perf_counter() + seconds
+
+    def work(t):
+        i = t
+        n = 0
+        while (fixed_searches is None and time.perf_counter() < deadline) or \
+                (fixed_searches is not None and n < fixed_searches):
+            j = i % len(cells)
+            b = orc.board_from_cells(cells[j], to_move[j], count[j])
+            p = O.params(sims_per_search, PRESET["c_puct"], PRESET["beta"], PRESET["planner_steps"],
+                         int(to_move[j]), PRESET["difficulty"], eval_nodes=1)
+            r = O.search(b, p, seed=12345 + j, game=j)     # ctypes releases the GIL
+            done[t] += sims_per_search
+            i += threads
+            n += 1
+            del r
+
+    t0 = time.perf_counter()
+    ths = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    dt = time.perf_counter() - t0
+    return sum(done) / dt, threads, sum(done), dt
+
+
+def config_dict(G, n_gpus, extra=None):
+    c = {"workload": "hard preset search: S=%d sims/position, c_puct=%.1f, beta=%.1f, planner_steps=%d, "
+                     "G=%d concurrent 15x15 games per GPU (BASELINE config 3); synthetic mid-game "
+                     "positions with %s stones" % (PRESET["sims"], PRESET["c_puct"], PRESET["beta"],
+                                                   PRESET["planner_steps"], G, "6/12/24/48/96/150"),
+         "games_per_gpu": G, "sims_per_position": PRESET["sims"], "parallelism": "games x%d" % n_gpus,
+         "l2_policy": "per-step working set (activations, trees) exceeds the 126 MB L2; no explicit flush",
+         "weights": "random init (torch default, seed 1234)"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+def run_reference(args):
+    """CPU arm: the reference's algorithm (oracle port) on all host cores; each step = one bounded
+    sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import workload
+    cells, tm, mc = workload.make_positions(256, seed=2026)
+    sims_ref = 2
+    threads = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        cpu_sample(cells, tm, mc, 0, sims_ref, threads, fixed_searches=1)
+    total, t_all = 0, 0.0
+    for _ in range(args.steps):
+        rate, th, n, dt = cpu_sample(cells, tm, mc, 0, sims_ref, threads, fixed_searches=2)
+        total += n
+        t_all += dt
+    value = total / t_all
+    sample = "%d threads x 2 searches x %d sims per step on the first positions of the workload" % (threads, sims_ref)
+    line = {"impl": "reference", "metric": "mcts_sims_per_sec", "value": value, "unit": "sims/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t_all / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args.games, args.gpus, {"note": "CPU arm: bounded sample per step"}),
+            "cpu_baseline": {"value": value, "unit": "sims/s", "cores": threads, "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": value, "unit": "sims/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_engine(args):
+    import torch
+    import engine
+    import workload
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    G, S = args.games, PRESET["sims"]
+    eng = engine.Engine(max_games=G, max_simulations=S, device=local, store_priors=True)
+    pv, gn, dq = synthetic_weights()
+    eng.set_pv_weights(pv)
+    eng.set_planner_weights(gn, dq)
+    cells, tm, mc = workload.make_positions(G, seed=2026 + rank)
+    boards = eng.boards_from_cells(cells, tm, mc)
+    ai = tm.copy()
+
+    def params(step):
+        return engine.make_params(S, PRESET["c_puct"], beta=PRESET["beta"],
+                                  planner_steps=PRESET["planner_steps"], difficulty=PRESET["difficulty"],
+                                  deterministic=False, seed=0xB200 + step, game_base=rank * G)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for w in range(args.warmup):
+        eng.search(boards, ai, params(1000 + w))
+    barrier()
+    eng.reset_counters()
+    eng.set_profiling(True)
+    eng.stage_times()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for k in range(args.steps):
+        eng.search(boards, ai, params(k))
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.finish()
+    stages = eng.stage_times()
+    eng.set_profiling(False)
+    cnt = eng.counters()
+    t_ms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    sims = torch.tensor([float(cnt["simulations"])], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sims, op=dist.ReduceOp.SUM)
+    ms_max, sims_total = t_ms.item(), sims.item()
+    value = sims_total / (ms_max / 1e3)
+
+    # ---- end to end through the host-buffer entry point (pinned host memory, copies timed)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()  # noqa: E731
+    h_cells, h_tm, h_mc, h_ai = pin(cells), pin(tm), pin(mc), pin(ai)
+    out = (pin(np.empty((G, 225), np.int32)), pin(np.empty((G, 225), np.float64)), pin(np.empty(G, np.int32)))
+    eng.search_host(h_cells, h_tm, h_mc, h_ai, params(2000), out)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        eng.search_host(h_cells, h_tm, h_mc, h_ai, params(3000 + k), out)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t_e = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+    e2e = world * G * S * args.steps / t_e.item()
+    h2d = G * (225 + 1 + 1 + 2)
+    d2h = G * (225 * 4 + 225 * 8 + 4)
+
+    if rank == 0:
+        peaks = load_peaks()
+        total_ms = sum(v[0] for v in stages.values())
+        dom = max(stages, key=lambda k: stages[k][0])
+        d_ms, d_launch = stages[dom]
+        share = {k: round(v[0] / total_ms, 4) for k, v in stages.items() if v[1]}
+        if dom in STAGE_FLOPS:
+            unit, f = STAGE_FLOPS[dom]
+            achieved = cnt[unit] * f / (d_ms / 1e3) / 1e12
+            roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"],
+                    "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"], "traffic": None}
+        else:
+            unit, by = STAGE_BYTES.get(dom, ("simulations", 0))
+            achieved = cnt[unit] * by / (d_ms / 1e3) / 1e9
+            roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
+                    "frac": achieved / peaks["hbm"], "traffic": None}
+        roof.update({"kernel": dom, "launches": d_launch, "avg_launch_ms": d_ms / max(d_launch, 1),
+                     "share_of_step": round(d_ms / total_ms, 4), "stage_share": share,
+                     "peak_source": peaks["source"] + (" (sustained bf16 cuBLAS)" if roof["bound"] == "tensor" else " (copy)")})
+        f_sim = (cnt["pv_evals"] * (F_PV_CONV0 + F_PV_TOWER + F_PV_HEADS) +
+                 cnt["planner_steps"] * (F_GN_CONVS + F_GN_HEAD + F_DQN)) / max(cnt["simulations"], 1)
+        cpu_rate, cores, n_cpu, dt_cpu = cpu_sample(cells[:256], tm[:256], mc[:256], args.cpu_seconds, 2)
+        line = {"metric": "mcts_sims_per_sec", "value": value, "unit": "sims/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": config_dict(G, world),
+                "clocks": clocks,
+                "e2e": {"value": e2e, "unit": "sims/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": cnt["kernel_launches"],
+                "roofline": roof,
+                "cpu_baseline": {"value": cpu_rate, "unit": "sims/s", "cores": cores, "kind": "port",
+                                 "sample": "%d sims in %.1f s: %d threads running 2-sim searches of the same "
+                                           "preset on the first 256 workload positions" % (n_cpu, dt_cpu, cores)},
+                "flops_per_sim": f_sim,
+                "tensor_frac_whole_step": value * f_sim / 1e12 / peaks["tf_sustained"] / world,
+                "counters": cnt}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--games", type=int, default=4096)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_engine(args)
+
+
+if __name__ == "__main__":
+    main()

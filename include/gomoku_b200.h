@@ -188,6 +188,28 @@ int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t *h_to_move
 int gz_get_tree(gz_handle h, int32_t g, int32_t cap, int32_t *h_parent, int32_t *h_move,
                 int32_t *h_visits, double *h_value, int32_t *n_nodes);
 
+/* ---- stage timing ---------------------------------------------------------------------------------- */
+/* CUDA-event timing of the engine's kernel groups on the launching stream.  When enabled, every
+ * group of launches inside gz_search / gz_rollout / gz_pv_forward / ... is bracketed by two events;
+ * gz_get_stage_times synchronises, accumulates elapsed milliseconds and launch counts per stage and
+ * clears the pending events.  Off by default (the events cost a few microseconds per wave). */
+enum {
+    GZ_STAGE_TREE = 0,         /* select / expand / backup */
+    GZ_STAGE_PV_CONV0 = 1,     /* 3 -> 128 input convolution (planes generated in-kernel) */
+    GZ_STAGE_PV_TOWER = 2,     /* the four 128 -> 128 3x3 convolutions (dominant FLOPs) */
+    GZ_STAGE_PV_HEADS = 3,     /* policy / value heads, softmax, prior */
+    GZ_STAGE_PLAN_SCORE = 4,   /* knowledge-search scoring + top-k */
+    GZ_STAGE_GN_CONVS = 5,     /* GraphNet convolutions */
+    GZ_STAGE_GN_HEAD = 6,      /* GraphNet head + softmax */
+    GZ_STAGE_DQN = 7,          /* OpponentDQN */
+    GZ_STAGE_PLAN_PICK = 8,    /* blend, explore roll, make_move */
+    GZ_STAGE_ROLLOUT = 9,      /* offensive-random tail */
+    GZ_STAGE_MISC = 10,        /* import / export / finalize */
+    GZ_N_STAGES = 12
+};
+int gz_set_profiling(gz_handle h, int32_t on);
+int gz_get_stage_times(gz_handle h, double *h_ms /*[GZ_N_STAGES]*/, int64_t *h_launches /*[GZ_N_STAGES]*/);
+
 /* ---- counters ---------------------------------------------------------------------------------- */
 int gz_get_counters(gz_handle h, gz_counters *out);
 int gz_reset_counters(gz_handle h);
