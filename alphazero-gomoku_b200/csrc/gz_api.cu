@@ -76,7 +76,11 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
     CK(dalloc(&s.board, G)); CK(dalloc(&s.leaf, G)); CK(dalloc(&s.need_eval, G));
     CK(dalloc(&s.steps, G)); CK(dalloc(&s.value, G)); CK(dalloc(&s.topk, G * kMaxTopK));
     CK(dalloc(&s.ntop, G));
-    for (int i = 0; i < 3; ++i) CK(dalloc(&e->act[i], G * 128 * kCells));
+    if (cfg->precision == 1) {
+        for (int i = 0; i < 3; ++i) CK(dalloc(&e->planes[i], G * 16 * kPlaneBytes + 2 * kGuardBytes));
+    } else {
+        for (int i = 0; i < 3; ++i) CK(dalloc(&e->act[i], G * 128 * kCells));
+    }
     CK(dalloc(&e->gn_logits, G * kCells)); CK(dalloc(&e->gn_policy, G * kCells));
     CK(dalloc(&e->dqn_q, G * kCells));
     CK(dalloc(&e->pv_logits, G * kCells)); CK(dalloc(&e->pv_probs, G * kCells));
@@ -102,7 +106,7 @@ extern "C" int gz_destroy(gz_handle h) {
                     e->sim.need_eval, e->sim.steps, e->sim.value, e->sim.topk, e->sim.ntop, e->act[0],
                     e->act[1], e->act[2], e->gn_logits, e->gn_policy, e->dqn_q, e->pv_logits,
                     e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
-                    e->tanh_table, e->weight_blob, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
+                    e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
     cudaStreamDestroy(e->own_stream);
@@ -155,6 +159,38 @@ void pack_head_conv(Packer &pk, const float *w, const float *b, int cout, int ci
 }
 }  // namespace
 
+static uint16_t f2bf(float f) {   // round to nearest even
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7F800000u) == 0x7F800000u) return (uint16_t)(u >> 16);
+    u += 0x7FFFu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+// conv weight [cout][cin][k][k] (+ BN) -> per K-step (tap, 64-channel chunk) a block
+// [8 channel groups][cout][8 channels] of bf16: K-major SWIZZLE_NONE core matrices for tcgen05.mma
+static void pack_conv_bf16(std::vector<uint16_t> &out, const float *w, const float *bn, int cout, int cin, int k) {
+    int T = k * k, chunks = cin / 64;
+    size_t base = out.size();
+    out.resize(base + (size_t)T * cin * cout);
+    for (int tap = 0; tap < T; ++tap)
+        for (int ch = 0; ch < chunks; ++ch)
+            for (int cgl = 0; cgl < 8; ++cgl)
+                for (int co = 0; co < cout; ++co) {
+                    double scale = bn ? (double)bn[co] / sqrt((double)bn[3 * cout + co] + 1e-5) : 1.0;
+                    for (int j = 0; j < 8; ++j) {
+                        int ci = ch * 64 + cgl * 8 + j;
+                        size_t o = base + ((((size_t)(tap * chunks + ch) * 8 + cgl) * cout + co) * 8 + j);
+                        out[o] = f2bf((float)((double)w[((size_t)co * cin + ci) * T + tap] * scale));
+                    }
+                }
+}
+static int upload_bytes(const void *src, size_t bytes, uint8_t **dev) {
+    if (*dev) { cudaFree(*dev); *dev = nullptr; }
+    CK(cudaMalloc((void **)dev, bytes));
+    CK(cudaMemcpy(*dev, src, bytes, cudaMemcpyHostToDevice));
+    return GZ_OK;
+}
+
 static int upload(Packer &pk, float **dev) {
     if (*dev) { cudaFree(*dev); *dev = nullptr; }
     CK(cudaMalloc((void **)dev, pk.host.size() * sizeof(float)));
@@ -197,6 +233,23 @@ extern "C" int gz_set_pv_weights(gz_handle h, const float *f, int64_t n) {
     w.vconv_w = d + o[14]; w.vconv_b = d + o[15];
     w.vfc1_wt = d + o[16]; w.vfc1_b = d + o[17];
     w.vfc2_w = d + ow2; w.vfc2_b = d + ob2;
+    {   // bf16 packs of the four tower convolutions
+        std::vector<uint16_t> bf;
+        const float *q = f + 3456 + 128 + 512;
+        size_t off[4];
+        for (int blk = 0; blk < 2; ++blk) {
+            const float *c1w = q, *c1b = q + 147456, *c2w = c1b + 128, *c2b = c2w + 147456;
+            const float *bn1 = c2b + 128, *bn2 = bn1 + 512;
+            off[2 * blk] = bf.size() * 2;
+            pack_conv_bf16(bf, c1w, bn1, 128, 128, 3);
+            off[2 * blk + 1] = bf.size() * 2;
+            pack_conv_bf16(bf, c2w, bn2, 128, 128, 3);
+            q = bn2 + 512;
+        }
+        rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.pv_blob);
+        if (rc) return rc;
+        for (int i = 0; i < 4; ++i) e->bw.pv_tower_w[i] = e->bw.pv_blob + off[i];
+    }
     e->have_pv = true;
     return GZ_OK;
 }
@@ -230,6 +283,18 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         }
         w.hconv_w = d + o[18]; w.hconv_b = d + o[19];
         w.hfc_wt = d + o[20]; w.hfc_b = d + o[21];
+        std::vector<uint16_t> bf;
+        size_t o3[4], o1[4];
+        const float *q = gnf + 1728 + 64;
+        for (int i = 0; i < 4; ++i) {
+            o3[i] = bf.size() * 2;
+            pack_conv_bf16(bf, q, nullptr, 64, 64, 3); q += 36864 + 64;
+            o1[i] = bf.size() * 2;
+            pack_conv_bf16(bf, q, nullptr, 64, 64, 1); q += 4096 + 64;
+        }
+        rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.gn_blob);
+        if (rc) return rc;
+        for (int i = 0; i < 4; ++i) { e->bw.gn_l3_w[i] = e->bw.gn_blob + o3[i]; e->bw.gn_l1_w[i] = e->bw.gn_blob + o1[i]; }
     }
     {
         Packer pk;
@@ -347,7 +412,7 @@ extern "C" int gz_pv_forward(gz_handle h, const gz_board *d_boards, int32_t G, f
     if (rc) return rc;
     if (!d_boards) return fail(GZ_ERR_ARG, "gz_pv_forward: null pointer");
     if (!e->have_pv) return fail(GZ_ERR_STATE, "gz_pv_forward: gz_set_pv_weights was not called");
-    nn_pv_forward_fp32(*e, d_boards, nullptr, G, d_logits, d_probs, d_value, nullptr, nullptr, strm(stream));
+    nn_pv_forward(*e, d_boards, nullptr, G, d_logits, d_probs, d_value, nullptr, nullptr, strm(stream));
     CKL();
     return GZ_OK;
 }
@@ -360,9 +425,22 @@ extern "C" int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, in
     if (rc) return rc;
     if (!d_boards) return fail(GZ_ERR_ARG, "gz_planner_nets_forward: null pointer");
     if (!e->have_planner) return fail(GZ_ERR_STATE, "gz_planner_nets_forward: planner weights not set");
-    nn_planner_forward_fp32(*e, d_boards, G, d_gn_logits ? d_gn_logits : e->gn_logits,
+    nn_planner_forward(*e, d_boards, G, d_gn_logits ? d_gn_logits : e->gn_logits,
                             d_gn_policy ? d_gn_policy : e->gn_policy, d_dqn_q ? d_dqn_q : e->dqn_q,
                             strm(stream));
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_debug_pv_layer(gz_handle h, const gz_board *d_boards, int32_t G, int32_t nlayers,
+                                 float *d_out, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_debug_pv_layer");
+    if (rc) return rc;
+    if (!d_boards || !d_out || nlayers < 0 || nlayers > 4) return fail(GZ_ERR_ARG, "gz_debug_pv_layer: bad argument");
+    if (!e->have_pv) return fail(GZ_ERR_STATE, "gz_debug_pv_layer: gz_set_pv_weights was not called");
+    if (e->cfg.precision == 1) nn_debug_pv_layer_bf16(*e, d_boards, G, nlayers, d_out, strm(stream));
+    else nn_debug_pv_layer_fp32(*e, d_boards, G, nlayers, d_out, strm(stream));
     CKL();
     return GZ_OK;
 }
@@ -381,7 +459,7 @@ extern "C" int gz_planner_move(gz_handle h, const gz_board *d_boards, const uint
     cudaStream_t s = strm(stream);
     int32_t *topk = d_topk ? d_topk : e->sim.topk;
     launch_planner_score(d_boards, d_ai_player, nullptr, G, c, step, topk, e->sim.ntop, d_scores2, s);
-    nn_planner_forward_fp32(*e, d_boards, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+    nn_planner_forward(*e, d_boards, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
     launch_planner_pick(const_cast<gz_board *>(d_boards), d_ai_player, nullptr, G, c, sim, step, topk,
                         e->sim.ntop, e->gn_policy, e->dqn_q, d_composed, d_move, false, nullptr, s);
     e->launches += 2;
@@ -410,7 +488,7 @@ static void run_playouts(Engine *e, int G, const SearchCfg &c, int sim, cudaStre
         launch_planner_score(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, k, e->sim.topk,
                              e->sim.ntop, nullptr, s);
         prof_end(*e, s);
-        nn_planner_forward_fp32(*e, e->sim.board, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+        nn_planner_forward(*e, e->sim.board, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
         prof_begin(*e, GZ_STAGE_PLAN_PICK, 1, s);
         launch_planner_pick(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, sim, -1, e->sim.topk,
                             e->sim.ntop, e->gn_policy, e->dqn_q, nullptr, nullptr, true, e->counters, s);
@@ -455,14 +533,14 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     launch_tree_init(*e, d_boards, d_ai, G, s);
     prof_end(*e, s);
     if (c.eval_nodes)
-        nn_pv_forward_fp32(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
+        nn_pv_forward(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
                            e->tree.prior, e->sim.leaf, s);
     for (int sim = 0; sim < c.S; ++sim) {
         prof_begin(*e, GZ_STAGE_TREE, 1, s);
         launch_tree_step(*e, G, c, sim, s);
         prof_end(*e, s);
         if (c.eval_nodes)
-            nn_pv_forward_fp32(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
+            nn_pv_forward(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
                                e->tree.prior, e->sim.leaf, s);
         run_playouts(e, G, c, sim, s);
     }

@@ -13,6 +13,10 @@ constexpr int kCells = 225;
 constexpr int kMaxTopK = 16;
 constexpr int kLogTableMax = 2048;
 constexpr int kTanhTableMax = 4096;
+// bf16 activation planes (gz_nn_bf16.cu): [board][channel group][288 positions][8 channels]
+constexpr int kPlanePos = 288;
+constexpr int kPlaneBytes = kPlanePos * 16;
+constexpr int kGuardBytes = 256;
 
 // fp32 network parameters on the device, BN folded, laid out for the FFMA kernels:
 // conv weights as [cin][tap][cout] (cout contiguous), linear weights transposed to [in][out].
@@ -40,6 +44,15 @@ struct DqnWeights {
     float *w1t, *b1;     // [675][256]
     float *w2t, *b2;     // [256][256]
     float *w3t, *b3;     // [256][225]
+};
+
+// bf16 tensor-core path: conv weights packed per K-step as [8 channel groups][cout][8 channels]
+// (K-major SWIZZLE_NONE core matrices), BN folded; biases and the first layer reuse the fp32 packs.
+struct Bf16Weights {
+    uint8_t *pv_tower_w[4];
+    uint8_t *gn_l3_w[4];
+    uint8_t *gn_l1_w[4];
+    uint8_t *pv_blob, *gn_blob;
 };
 
 // Flat SoA tree storage, tree g owns slots [g*cap, (g+1)*cap); node 0 is the root.
@@ -81,6 +94,8 @@ struct Engine {
     PvWeights pv;
     GraphNetWeights gn;
     DqnWeights dqn;
+    Bf16Weights bw;
+    uint8_t *planes[3];   // bf16 activation planes, [G][16][288][8] + guards (precision 1)
     void *weight_blob;    // single allocation backing all weights
     double *log_table;    // device
     double *tanh_table;   // device
@@ -158,5 +173,25 @@ void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active
                         const int32_t *prior_slot, cudaStream_t s);
 void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn_logits,
                              float *gn_policy, float *dqn_q, cudaStream_t s);
+
+// networks, bf16 tcgen05 path (gz_nn_bf16.cu)
+void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
+                        float *logits, float *probs, float *value, float *prior_out,
+                        const int32_t *prior_slot, cudaStream_t s);
+void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s);
+void nn_debug_planes_to_nchw(Engine &e, int which, int C, int G, float *out, cudaStream_t s);
+// heads reading bf16 planes, and the planner tail (GraphNet head + DQN) shared by both paths (gz_nn_fp32.cu)
+void nn_pv_heads_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards,
+                             const uint8_t *active, int G, float *logits, float *probs, float *value,
+                             float *prior_out, const int32_t *prior_slot, cudaStream_t s);
+void nn_planner_tail_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards, int G,
+                                 float *gn_logits, float *gn_policy, float *dqn_q, cudaStream_t s);
+void nn_debug_pv_layer_bf16(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s);
+void nn_debug_pv_layer_fp32(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s);
+// precision dispatch
+void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
+                   float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s);
+void nn_planner_forward(Engine &e, const gz_board *boards, int G, float *gn_logits, float *gn_policy,
+                        float *dqn_q, cudaStream_t s);
 
 }  // namespace gz

@@ -1,0 +1,336 @@
+// gz_nn_bf16.cu -- bf16 tensor-core (tcgen05 / TMEM) forward of the convolution stacks: the
+// throughput mode of AlphaZeroGomokuNet (neural_network.py:132-159) and GraphNet
+// (bg_planner.py:50-56).  fp32 accumulation in tensor memory, bf16 activations between layers.
+//
+// Activation layout in HBM ("planes"): [board][channel group of 8][288 positions][8 channels] bf16.
+// A plane is the 15x15 board on an 18-row x 16-column pitch: plane row 0 and rows 16,17 and column
+// 15 are zero padding, board cell (r,c) sits at position 16*(r+1)+c.  With that pitch a 3x3 tap
+// (dy,dx) is the constant position offset 16*dy+dx, so the implicit-GEMM A operand of every tap is
+// the SAME shared-memory slab read at a different row offset.  One channel group of one position
+// is 16 bytes = one row of a UMMA core matrix, and 8 consecutive positions are 128 contiguous bytes
+// = one K-major SWIZZLE_NONE core matrix at ANY row offset; no im2col, no tensor maps, no swizzle:
+// the slab of a board is fetched with one 1-D bulk copy (UBLKCP) per channel group.
+//
+// Tile = one board = M 256 (two UMMA M=128 halves: plane positions [16,144) and [144,272)),
+// N = all output channels, K = taps x input channels in steps of 64.  Persistent CTAs (one per SM):
+//   warp 0    producer: activation slab (double buffered) + weight K-steps (ring, or resident when
+//             the whole layer fits in shared memory)
+//   warp 1    single-thread tcgen05.mma issuer; accumulators double buffered in TMEM
+//   warps 2-5 epilogue: tcgen05.ld, bias (+ residual) + ReLU, zero the padding positions, pack to
+//             bf16, 16-byte coalesced stores
+#include "gz_engine.h"
+#include "gz_tcgen05.cuh"
+
+namespace gz {
+
+template <int CIN, int COUT, int TAPS, bool RESIDENT>
+struct ConvCfg {
+    static constexpr int CG = CIN / 8;                       // channel groups of the input
+    static constexpr int CHUNKS = CIN / 64;                  // 64-channel K chunks per tap
+    static constexpr int KSTEPS = TAPS * CHUNKS;
+    static constexpr int SLAB_ROWS = TAPS == 9 ? 290 : 256;  // positions [-1,289) or [16,272)
+    static constexpr int SLAB_BYTES = CG * SLAB_ROWS * 16;
+    static constexpr int WSTEP_BYTES = 8 * COUT * 16;        // one K-step of weights: [8 cg][COUT][8]
+    static constexpr int NSTAGE = RESIDENT ? KSTEPS : 4;
+    static constexpr int W_BYTES = NSTAGE * WSTEP_BYTES;
+    static constexpr int TCOLS = 4 * COUT;                   // 2 buffers x 2 halves x COUT fp32 columns
+    static constexpr int SMEM = 2 * SLAB_BYTES + W_BYTES + COUT * 4 + 256 + 128;
+};
+
+template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL>
+__global__ void __launch_bounds__(192, 1)
+k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w_packed,
+            const float *__restrict__ bias, const uint8_t *__restrict__ res_planes,
+            uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G) {
+    using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *slab = smem;                                   // [2][SLAB_BYTES]
+    uint8_t *wbuf = smem + 2 * C::SLAB_BYTES;               // [NSTAGE][WSTEP_BYTES]
+    float *sbias = reinterpret_cast<float *>(wbuf + C::W_BYTES);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(sbias) + COUT * 4);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *acc_full = bars + 4, *acc_empty = bars + 6;
+    uint64_t *b_full = bars + 8, *b_empty = bars + 8 + 4;   // ring (streaming) or b_full[0] = "resident loaded"
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16 + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&a_full[i], 1);
+            ptx::mbar_init(&a_empty[i], 1);
+            ptx::mbar_init(&acc_full[i], 1);
+            ptx::mbar_init(&acc_empty[i], 4);
+        }
+        for (int i = 0; i < 4; ++i) {
+            ptx::mbar_init(&b_full[i], 1);
+            ptx::mbar_init(&b_empty[i], 1);
+        }
+        ptx::fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < COUT; i += blockDim.x) sbias[i] = bias[i];
+    if (warp == 1) ptx::tmem_alloc<C::TCOLS>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= producer =================
+        if (lane == 0) {
+            if (RESIDENT) {
+                ptx::mbar_expect_tx(&b_full[0], C::KSTEPS * C::WSTEP_BYTES);
+                for (int ks = 0; ks < C::KSTEPS; ++ks)
+                    ptx::bulk_g2s(wbuf + ks * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES,
+                                  C::WSTEP_BYTES, &b_full[0]);
+            }
+            uint32_t it = 0, wstage = 0, wphase = 0;
+            for (int b = blockIdx.x; b < G; b += gridDim.x) {
+                if (active && !active[b]) continue;
+                const int ab = it & 1;
+                ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+                ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
+                const uint8_t *src = in_planes + kGuardBytes + (size_t)b * C::CG * kPlaneBytes +
+                                     (TAPS == 9 ? -16 : 256);
+                for (int cg = 0; cg < C::CG; ++cg)
+                    ptx::bulk_g2s(slab + ab * C::SLAB_BYTES + cg * C::SLAB_ROWS * 16,
+                                  src + (size_t)cg * kPlaneBytes, C::SLAB_ROWS * 16, &a_full[ab]);
+                if (!RESIDENT) {
+                    for (int ks = 0; ks < C::KSTEPS; ++ks) {
+                        ptx::mbar_wait(&b_empty[wstage], wphase ^ 1);
+                        ptx::mbar_expect_tx(&b_full[wstage], C::WSTEP_BYTES);
+                        ptx::bulk_g2s(wbuf + wstage * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES,
+                                      C::WSTEP_BYTES, &b_full[wstage]);
+                        if (++wstage == 4) { wstage = 0; wphase ^= 1; }
+                    }
+                }
+                ++it;
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(128, COUT);
+            constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = COUT * 16;
+            if (RESIDENT) ptx::mbar_wait(&b_full[0], 0);
+            uint32_t it = 0, wstage = 0, wphase = 0;
+            for (int b = blockIdx.x; b < G; b += gridDim.x) {
+                if (active && !active[b]) continue;
+                const int ab = it & 1;
+                const uint32_t par = (it >> 1) & 1;
+                ptx::mbar_wait(&acc_empty[ab], par ^ 1);
+                ptx::mbar_wait(&a_full[ab], par);
+                ptx::tc_fence_after();
+                const uint32_t slab_addr = ptx::smem_u32(slab + ab * C::SLAB_BYTES);
+                const uint32_t acc = tmem_base + ab * 2 * COUT;
+                for (int ks = 0; ks < C::KSTEPS; ++ks) {
+                    const int tap = ks / C::CHUNKS, chunk = ks - tap * C::CHUNKS;
+                    const int rowoff = TAPS == 9 ? 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1) : 0;
+                    uint32_t w_addr;
+                    if (RESIDENT) {
+                        w_addr = ptx::smem_u32(wbuf + ks * C::WSTEP_BYTES);
+                    } else {
+                        ptx::mbar_wait(&b_full[wstage], wphase);
+                        ptx::tc_fence_after();
+                        w_addr = ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES);
+                    }
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            uint32_t a_addr = slab_addr + ((chunk * 8 + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h) * 16;
+                            uint32_t b_addr = w_addr + 2 * k * LBO_B;
+                            ptx::umma_bf16(acc + h * COUT, ptx::make_desc(a_addr, LBO_A, 128),
+                                           ptx::make_desc(b_addr, LBO_B, 128), idesc, (ks | k) != 0);
+                        }
+                    }
+                    if (!RESIDENT) {
+                        ptx::umma_commit(&b_empty[wstage]);
+                        if (++wstage == 4) { wstage = 0; wphase ^= 1; }
+                    }
+                }
+                ptx::umma_commit(&a_empty[ab]);
+                ptx::umma_commit(&acc_full[ab]);
+                ++it;
+            }
+        }
+    } else {
+        // ================= epilogue (warps 2..5) =================
+        const int q = warp & 3;                 // TMEM lane quadrant this warp may read
+        uint32_t it = 0;
+        for (int b = blockIdx.x; b < G; b += gridDim.x) {
+            if (active && !active[b]) continue;
+            const int ab = it & 1;
+            ptx::mbar_wait(&acc_full[ab], (it >> 1) & 1);
+            ptx::tc_fence_after();
+            const size_t obase = kGuardBytes + (size_t)b * (COUT / 8) * kPlaneBytes;
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                const int pos = 16 + 128 * h + 32 * q + lane;
+                const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+                const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + ab * 2 * COUT + h * COUT;
+#pragma unroll 1
+                for (int c0 = 0; c0 < COUT; c0 += 16) {
+                    float v[16];
+                    ptx::tmem_ld16(taddr + c0, v);
+                    const size_t o0 = obase + (size_t)(c0 / 8) * kPlaneBytes + (size_t)pos * 16;
+                    if (RESIDUAL) {
+                        uint4 r0 = *reinterpret_cast<const uint4 *>(res_planes + o0);
+                        uint4 r1 = *reinterpret_cast<const uint4 *>(res_planes + o0 + kPlaneBytes);
+                        const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            v[2 * i] += __uint_as_float(rr[i] << 16);
+                            v[2 * i + 1] += __uint_as_float(rr[i] & 0xFFFF0000u);
+                        }
+                    }
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float x0 = fmaxf(v[2 * i] + sbias[c0 + 2 * i], 0.f);
+                        float x1 = fmaxf(v[2 * i + 1] + sbias[c0 + 2 * i + 1], 0.f);
+                        pk[i] = valid ? ptx::pack_bf16(x0, x1) : 0u;
+                    }
+                    *reinterpret_cast<uint4 *>(out_planes + o0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4 *>(out_planes + o0 + kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&acc_empty[ab]);
+            ++it;
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<C::TCOLS>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------
+// First layer (3 input planes generated from the bitboards, 3x3, folded BN, ReLU) on CUDA cores:
+// 0.6 % of the network FLOPs and its inputs are single bits, so it is a table-sum per position.
+// One CTA per board, thread = one plane position in [16,272); writes bf16 planes.
+template <int COUT>
+__global__ void __launch_bounds__(256)
+k_conv0_planes(const gz_board *__restrict__ boards, const uint8_t *__restrict__ active,
+               const float *__restrict__ w /*[27][COUT]*/, const float *__restrict__ bias,
+               uint8_t *__restrict__ out_planes) {
+    __shared__ __align__(16) float sw[27 * COUT];
+    __shared__ float sb[COUT];
+    __shared__ uint32_t sbits[2][8];
+    const int b = blockIdx.x;
+    if (active && !active[b]) return;
+    for (int i = threadIdx.x; i < 27 * COUT; i += 256) sw[i] = w[i];
+    for (int i = threadIdx.x; i < COUT; i += 256) sb[i] = bias[i];
+    if (threadIdx.x < 16) sbits[threadIdx.x >> 3][threadIdx.x & 7] = boards[b].stones[threadIdx.x >> 3][threadIdx.x & 7];
+    __syncthreads();
+    const int pos = 16 + threadIdx.x;
+    const int r = (pos >> 4) - 1, c = pos & 15;
+    const bool valid = c != 15 && r <= 14;
+    // 27 input bits: plane-major (black, white, empty) x tap (ky*3+kx), as the [ci][tap] weight order
+    uint32_t inbits = 0;
+    if (valid) {
+        for (int t = 0; t < 9; ++t) {
+            int rr = r + t / 3 - 1, cc = c + t % 3 - 1;
+            if (rr < 0 || rr > 14 || cc < 0 || cc > 14) continue;   // zero padding of the conv
+            int p = (rr << 4) | cc;
+            uint32_t bl = sbits[0][p >> 5] >> (p & 31) & 1u, wh = sbits[1][p >> 5] >> (p & 31) & 1u;
+            inbits |= bl << t | wh << (9 + t) | (1u - (bl | wh)) << (18 + t);
+        }
+    }
+    const size_t obase = kGuardBytes + (size_t)b * (COUT / 8) * kPlaneBytes + (size_t)pos * 16;
+#pragma unroll 1
+    for (int cg = 0; cg < COUT / 8; ++cg) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = sb[cg * 8 + j];
+        for (int t = 0; t < 27; ++t) {
+            if (!(inbits >> t & 1u)) continue;
+            const float4 *wp = reinterpret_cast<const float4 *>(&sw[t * COUT + cg * 8]);
+            float4 w0 = wp[0], w1 = wp[1];
+            acc[0] += w0.x; acc[1] += w0.y; acc[2] += w0.z; acc[3] += w0.w;
+            acc[4] += w1.x; acc[5] += w1.y; acc[6] += w1.z; acc[7] += w1.w;
+        }
+        uint32_t pk[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            pk[j] = valid ? ptx::pack_bf16(fmaxf(acc[2 * j], 0.f), fmaxf(acc[2 * j + 1], 0.f)) : 0u;
+        *reinterpret_cast<uint4 *>(out_planes + obase + (size_t)cg * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    }
+}
+
+// bf16 planes -> fp32 NCHW [G][C][225] (debug / parity inspection, and the input of the fp32 heads)
+__global__ void __launch_bounds__(256)
+k_planes_to_nchw(const uint8_t *__restrict__ planes, int C, const uint8_t *__restrict__ active,
+                 float *__restrict__ out) {
+    const int b = blockIdx.x;
+    if (active && !active[b]) return;
+    for (int i = threadIdx.x; i < C * kCells; i += 256) {
+        int ch = i / kCells, cell = i - ch * kCells;
+        int pos = 16 * (cell / 15 + 1) + cell % 15;
+        const uint16_t *p = reinterpret_cast<const uint16_t *>(planes + kGuardBytes +
+            ((size_t)b * (C / 8) + ch / 8) * kPlaneBytes + (size_t)pos * 16) + (ch & 7);
+        out[(size_t)b * C * kCells + i] = __uint_as_float((uint32_t)(*p) << 16);
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------------------
+template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL>
+static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const float *bias,
+                        const uint8_t *res, uint8_t *out, const uint8_t *active, int G, cudaStream_t s) {
+    using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
+    auto kern = k_conv_umma<CIN, COUT, TAPS, RESIDENT, RESIDUAL>;
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        configured = true;
+    }
+    int grid = G < e.sm_count ? G : e.sm_count;
+    kern<<<grid, 192, C::SMEM, s>>>(in, w, bias, res, out, active, G);
+}
+
+void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
+                        float *logits, float *probs, float *value, float *prior_out,
+                        const int32_t *prior_slot, cudaStream_t s) {
+    const Bf16Weights &w = e.bw;
+    uint8_t *p0 = e.planes[0], *p1 = e.planes[1], *p2 = e.planes[2];
+    prof_begin(e, GZ_STAGE_PV_CONV0, 1, s);
+    k_conv0_planes<128><<<G, 256, 0, s>>>(boards, active, e.pv.conv0.w, e.pv.conv0.b, p0);
+    prof_end(e, s);
+    prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
+    launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s);
+    launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s);
+    launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s);
+    launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s);
+    prof_end(e, s);
+    nn_pv_heads_from_planes(e, p0, boards, active, G, logits, probs, value, prior_out, prior_slot, s);
+}
+
+void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s) {
+    const Bf16Weights &w = e.bw;
+    uint8_t *p0 = e.planes[0], *p1 = e.planes[1];
+    prof_begin(e, GZ_STAGE_GN_CONVS, 9, s);
+    k_conv0_planes<64><<<G, 256, 0, s>>>(boards, active, e.gn.embed.w, e.gn.embed.b, p0);
+    for (int i = 0; i < 4; ++i) {
+        launch_conv<64, 64, 9, true, false>(e, p0, w.gn_l3_w[i], e.gn.l3[i].b, nullptr, p1, active, G, s);
+        launch_conv<64, 64, 1, true, false>(e, p1, w.gn_l1_w[i], e.gn.l1[i].b, nullptr, p0, active, G, s);
+    }
+    prof_end(e, s);
+}
+
+void nn_debug_planes_to_nchw(Engine &e, int which, int C, int G, float *out, cudaStream_t s) {
+    k_planes_to_nchw<<<G, 256, 0, s>>>(e.planes[which], C, nullptr, out);
+}
+
+// Output of the first `nlayers` tower convolutions (0 = the input convolution only) as fp32 NCHW.
+void nn_debug_pv_layer_bf16(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s) {
+    const Bf16Weights &w = e.bw;
+    uint8_t *p0 = e.planes[0], *p1 = e.planes[1], *p2 = e.planes[2];
+    k_conv0_planes<128><<<G, 256, 0, s>>>(boards, nullptr, e.pv.conv0.w, e.pv.conv0.b, p0);
+    int last = 0;
+    if (nlayers >= 1) { launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, nullptr, G, s); last = 1; }
+    if (nlayers >= 2) { launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, nullptr, G, s); last = 2; }
+    if (nlayers >= 3) { launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, nullptr, G, s); last = 1; }
+    if (nlayers >= 4) { launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, nullptr, G, s); last = 0; }
+    k_planes_to_nchw<<<G, 256, 0, s>>>(e.planes[last], 128, nullptr, out);
+}
+
+}  // namespace gz

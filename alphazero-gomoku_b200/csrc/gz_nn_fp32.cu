@@ -105,7 +105,7 @@ k_conv(const float *__restrict__ in, const gz_board *__restrict__ boards,
 // node prior: probabilities gathered over the legal cells and renormalised (ai_agent.py:564-582).
 constexpr int kHeadNB = 4;
 
-template <int C, bool VALUE>
+template <int C, bool VALUE, bool PLANES>
 __global__ void __launch_bounds__(256)
 k_heads(const float *__restrict__ x, const gz_board *__restrict__ boards,
         const uint8_t *__restrict__ active, int G, const float *__restrict__ pconv_w,
@@ -132,7 +132,24 @@ k_heads(const float *__restrict__ x, const gz_board *__restrict__ boards,
         for (int nb = 0; nb < kHeadNB; ++nb) {
             int b = b0 + nb;
             float p0 = pconv_b[0], p1 = pconv_b[1], v0 = VALUE ? vconv_b[0] : 0.f;
-            if (b < G) {
+            if (b < G && PLANES) {
+                // bf16 planes [board][C/8][288][8]: one 16-byte load gives 8 channels of this cell
+                const int pos = 16 * (t / 15 + 1) + t % 15;
+                const uint8_t *pb = reinterpret_cast<const uint8_t *>(x) + kGuardBytes +
+                                    (size_t)b * (C / 8) * kPlaneBytes + (size_t)pos * 16;
+                for (int cg = 0; cg < C / 8; ++cg) {
+                    uint4 u = *reinterpret_cast<const uint4 *>(pb + (size_t)cg * kPlaneBytes);
+                    const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float xv = __uint_as_float((j & 1) ? (uw[j >> 1] & 0xFFFF0000u) : (uw[j >> 1] << 16));
+                        int c = cg * 8 + j;
+                        p0 = fmaf(pconv_w[2 * c], xv, p0);
+                        p1 = fmaf(pconv_w[2 * c + 1], xv, p1);
+                        if (VALUE) v0 = fmaf(vconv_w[c], xv, v0);
+                    }
+                }
+            } else if (b < G) {
                 const float *xb = x + (size_t)b * C * kCells + t;
                 for (int c = 0; c < C; ++c) {
                     float xv = xb[(size_t)c * kCells];
@@ -296,7 +313,7 @@ void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active
     k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, active, w.tower[3].w, w.tower[3].b, a2, a0);
     prof_end(e, s);
     prof_begin(e, GZ_STAGE_PV_HEADS, 1, s);
-    k_heads<128, true><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
+    k_heads<128, true, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
         a0, boards, active, G, w.pconv_w, w.pconv_b, w.pfc_wt, w.pfc_b, w.vconv_w, w.vconv_b,
         w.vfc1_wt, w.vfc1_b, w.vfc2_w, w.vfc2_b, logits, probs, value, prior_out, prior_slot,
         e.tree.cap, prior_slot ? e.tree.vhead : nullptr);
@@ -316,13 +333,66 @@ void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn
     }
     prof_end(e, s);
     prof_begin(e, GZ_STAGE_GN_HEAD, 1, s);
-    k_heads<64, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
+    k_heads<64, false, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
         a0, boards, nullptr, G, w.hconv_w, w.hconv_b, w.hfc_wt, w.hfc_b, nullptr, nullptr, nullptr,
         nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr, nullptr, nullptr, 0, nullptr);
     prof_end(e, s);
     prof_begin(e, GZ_STAGE_DQN, 1, s);
     k_dqn<<<(G + kDqnNB - 1) / kDqnNB, 256, 0, s>>>(boards, nullptr, G, e.dqn, dqn_q);
     prof_end(e, s);
+}
+
+void nn_debug_pv_layer_fp32(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s) {
+    const PvWeights &w = e.pv;
+    float *a0 = e.act[0], *a1 = e.act[1], *a2 = e.act[2], *last = a0;
+    k_conv<3, 128, 3, true, false, true><<<G, 256, 0, s>>>(nullptr, boards, nullptr, w.conv0.w, w.conv0.b, nullptr, a0);
+    if (nlayers >= 1) { k_conv<128, 128, 3, false, false, true><<<G, 256, 0, s>>>(a0, nullptr, nullptr, w.tower[0].w, w.tower[0].b, nullptr, a1); last = a1; }
+    if (nlayers >= 2) { k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, nullptr, w.tower[1].w, w.tower[1].b, a0, a2); last = a2; }
+    if (nlayers >= 3) { k_conv<128, 128, 3, false, false, true><<<G, 256, 0, s>>>(a2, nullptr, nullptr, w.tower[2].w, w.tower[2].b, nullptr, a1); last = a1; }
+    if (nlayers >= 4) { k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, nullptr, w.tower[3].w, w.tower[3].b, a2, a0); last = a0; }
+    cudaMemcpyAsync(out, last, sizeof(float) * (size_t)G * 128 * kCells, cudaMemcpyDeviceToDevice, s);
+}
+
+void nn_pv_heads_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards,
+                             const uint8_t *active, int G, float *logits, float *probs, float *value,
+                             float *prior_out, const int32_t *prior_slot, cudaStream_t s) {
+    const PvWeights &w = e.pv;
+    prof_begin(e, GZ_STAGE_PV_HEADS, 1, s);
+    k_heads<128, true, true><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
+        reinterpret_cast<const float *>(planes), boards, active, G, w.pconv_w, w.pconv_b, w.pfc_wt,
+        w.pfc_b, w.vconv_w, w.vconv_b, w.vfc1_wt, w.vfc1_b, w.vfc2_w, w.vfc2_b, logits, probs, value,
+        prior_out, prior_slot, e.tree.cap, prior_slot ? e.tree.vhead : nullptr);
+    prof_end(e, s);
+}
+
+void nn_planner_tail_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards, int G,
+                                 float *gn_logits, float *gn_policy, float *dqn_q, cudaStream_t s) {
+    const GraphNetWeights &w = e.gn;
+    prof_begin(e, GZ_STAGE_GN_HEAD, 1, s);
+    k_heads<64, false, true><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
+        reinterpret_cast<const float *>(planes), boards, nullptr, G, w.hconv_w, w.hconv_b, w.hfc_wt,
+        w.hfc_b, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr,
+        nullptr, nullptr, 0, nullptr);
+    prof_end(e, s);
+    prof_begin(e, GZ_STAGE_DQN, 1, s);
+    k_dqn<<<(G + kDqnNB - 1) / kDqnNB, 256, 0, s>>>(boards, nullptr, G, e.dqn, dqn_q);
+    prof_end(e, s);
+}
+
+void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
+                   float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s) {
+    if (e.cfg.precision == 1) nn_pv_forward_bf16(e, boards, active, G, logits, probs, value, prior_out, prior_slot, s);
+    else nn_pv_forward_fp32(e, boards, active, G, logits, probs, value, prior_out, prior_slot, s);
+}
+
+void nn_planner_forward(Engine &e, const gz_board *boards, int G, float *gn_logits, float *gn_policy,
+                        float *dqn_q, cudaStream_t s) {
+    if (e.cfg.precision == 1) {
+        nn_graphnet_convs_bf16(e, boards, nullptr, G, s);
+        nn_planner_tail_from_planes(e, e.planes[0], boards, G, gn_logits, gn_policy, dqn_q, s);
+    } else {
+        nn_planner_forward_fp32(e, boards, G, gn_logits, gn_policy, dqn_q, s);
+    }
 }
 
 }  // namespace gz

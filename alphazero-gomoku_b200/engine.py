@@ -21,7 +21,7 @@ EXPORTS = [
     "gz_dqn_param_count", "gz_boards_from_cells", "gz_boards_to_cells", "gz_make_moves",
     "gz_board_ops", "gz_pv_forward", "gz_planner_nets_forward", "gz_planner_move",
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
-    "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_get_stage_times",
+    "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_get_stage_times", "gz_debug_pv_layer",
 ]
 
 STAGES = ["tree", "pv_conv0", "pv_tower", "pv_heads", "planner_score", "gn_convs", "gn_head", "dqn",
@@ -196,6 +196,12 @@ class Engine:
         self._ck(self.L.gz_pv_forward(self.h, _ptr(boards), G, _ptr(logits), _ptr(probs), _ptr(value),
                                       self._stream()))
         return logits, probs, value
+
+    def debug_pv_layer(self, boards, nlayers):
+        G = boards.shape[0]
+        out = self.torch.empty((G, 128, 225), dtype=self.torch.float32, device=self.device)
+        self._ck(self.L.gz_debug_pv_layer(self.h, _ptr(boards), G, int(nlayers), _ptr(out), self._stream()))
+        return out
 
     def planner_nets_forward(self, boards):
         t = self.torch

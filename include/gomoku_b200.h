@@ -144,6 +144,12 @@ int gz_pv_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_log
 int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_gn_logits,
                             float *d_gn_policy, float *d_dqn_q, void *stream);
 
+/* Inspection: output of the input convolution (nlayers = 0) or of the first nlayers (1..4) tower
+ * convolutions of AlphaZeroGomokuNet in the handle's precision, as fp32 NCHW d_out f32[G,128,225]
+ * (neural_network.py:142-146, :85-91).  Used by the per-layer parity tests. */
+int gz_debug_pv_layer(gz_handle h, const gz_board *d_boards, int32_t G, int32_t nlayers, float *d_out,
+                      void *stream);
+
 /* ---- planner move (bg_planner.py:232-269) --------------------------------------------------- */
 /* One BGPlannerAI.get_move per board.  d_ai_player u8[G] is the planner's fixed colour
  * (ai_agent.py:60).  Outputs (any may be NULL):

@@ -1,0 +1,95 @@
+"""bf16 tcgen05 network path (precision=1) on the B200: per-layer against the fp32 FFMA path, final
+outputs against the reference goldens within the north-star's 2e-2, and searches whose trees must
+not depend on the network precision (the reference never reads the network output)."""
+import numpy as np
+import pytest
+
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engines(weights):
+    import engine
+    out = []
+    for prec in (0, 1):
+        e = engine.Engine(max_games=256, max_simulations=200, precision=prec)
+        e.set_pv_weights(weights["pv"])
+        e.set_planner_weights(weights["graphnet"], weights["dqn"])
+        out.append(e)
+    yield out
+    for e in out:
+        e.close()
+
+
+def _boards(e, cells):
+    stones = (cells != 0).sum(1)
+    return e.boards_from_cells(cells, 1 + stones % 2, stones)
+
+
+def test_tower_layer_by_layer(engines):
+    f32, b16 = engines
+    g = golden("nets")
+    cells = np.concatenate([g["cells"]] * 6)[:200]      # > 148 boards: every CTA loops over tiles
+    for n in range(5):
+        a = f32.debug_pv_layer(_boards(f32, cells), n).cpu().numpy()
+        b = b16.debug_pv_layer(_boards(b16, cells), n).cpu().numpy()
+        scale = np.abs(a).max()
+        err = np.abs(a - b).max()
+        assert err <= 2e-2 * max(scale, 1.0), (n, err, scale)
+        assert np.array_equal(b[:36], b[36:72])          # same board -> same result on another CTA
+
+
+def test_pv_outputs_vs_reference(engines):
+    _, b16 = engines
+    g = golden("nets")
+    lg, pr, v = (t.cpu().numpy() for t in b16.pv_forward(_boards(b16, g["cells"])))
+    assert np.max(np.abs(lg - g["logits"])) < 2e-2          # north_star: 2e-2 in bf16
+    assert np.max(np.abs(pr - g["probs"])) < 2e-2
+    assert np.max(np.abs(v - g["value"])) < 2e-2
+
+
+def test_planner_nets_vs_reference(engines):
+    _, b16 = engines
+    g = golden("nets")
+    gl, gp, q = (t.cpu().numpy() for t in b16.planner_nets_forward(_boards(b16, g["cells"])))
+    # GraphNet logits are O(3) with the spread-out test weights: 2e-2 relative to their scale
+    assert np.max(np.abs(gl - g["gn_logits"])) < 2e-2 * max(1.0, np.abs(g["gn_logits"]).max())
+    assert np.max(np.abs(q - g["dqn_q"])) < 1e-4            # the DQN stays fp32
+
+
+def test_search_trees_do_not_depend_on_precision(engines):
+    import engine
+    f32, b16 = engines
+    g = golden("tiers")
+    sel = np.arange(0, len(g["cells"]), 3)
+    p = engine.make_params(120, 1.6, beta=0.2, difficulty="medium", deterministic=True)
+    outs = []
+    for e in (f32, b16):
+        boards = e.boards_from_cells(g["cells"][sel], g["to_move"][sel], g["move_count"][sel])
+        cv, cval, best = e.search(boards, g["to_move"][sel], p)
+        outs.append((cv.cpu().numpy(), cval.cpu().numpy(), best.cpu().numpy()))
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b)
+
+
+def test_det_b_search_bf16_vs_reference(engines):
+    """Planner-guided searches in bf16: the blended pick may flip on near-ties, so allow a few trees
+    to differ; the rest must be bit-exact against the reference goldens."""
+    import engine
+    _, b16 = engines
+    g = golden("mcts_planner")
+    bad = 0
+    for i in range(len(g["sims"])):
+        p = engine.make_params(int(g["sims"][i]), float(g["c_puct"][i]), beta=float(g["beta"][i]),
+                               planner_steps=int(g["planner_steps"][i]), difficulty=str(g["difficulty"][i]),
+                               deterministic=True)
+        boards = b16.boards_from_cells(g["cells"][i][None], [g["to_move"][i]], [g["move_count"][i]])
+        b16.search(boards, [g["ai_player"][i]], p)
+        t = b16.get_tree(0)
+        n = int(g["n_nodes"][i])
+        if not (len(t["visits"]) == n and np.array_equal(t["visits"], g["visits"][i][:n])
+                and np.array_equal(t["value"], g["value"][i][:n])):
+            bad += 1
+    assert bad <= len(g["sims"]) // 3, bad
