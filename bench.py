@@ -192,7 +192,8 @@ def run_engine(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     G, S = args.games, PRESET["sims"]
-    eng = engine.Engine(max_games=G, max_simulations=S, device=local, store_priors=True)
+    eng = engine.Engine(max_games=G, max_simulations=S, device=local, store_priors=True,
+                        precision=1 if args.precision == "bf16" else 0)
     pv, gn, dq = synthetic_weights()
     eng.set_pv_weights(pv)
     eng.set_planner_weights(gn, dq)
@@ -280,7 +281,7 @@ def run_engine(args):
         cpu_rate, cores, n_cpu, dt_cpu = cpu_sample(cells[:256], tm[:256], mc[:256], args.cpu_seconds, 2)
         line = {"metric": "mcts_sims_per_sec", "value": value, "unit": "sims/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
                 "data": "synthetic", "config": config_dict(G, world),
                 "clocks": clocks,
                 "e2e": {"value": e2e, "unit": "sims/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
@@ -305,6 +306,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--games", type=int, default=4096)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
+                    help="network arithmetic: bf16 tcgen05 (timed mode) or fp32 FFMA (parity mode)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
