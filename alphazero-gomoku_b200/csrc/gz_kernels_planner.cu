@@ -6,6 +6,7 @@
 // Integer-ALU bound; per board-step 80 B in, <= 72 B out.
 #include "gz_engine.h"
 #include "gz_warp.cuh"
+#include "gz_lines.cuh"
 
 namespace gz {
 
@@ -29,18 +30,39 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
     }
     BB black = bb_load(b.stones[0]), white = bb_load(b.stones[1]);
     BB empty = bb_empty_cells(black, white);
-    int a = ai_player[g];
-    const BB a_st = (a == 1) ? black : white;
+    const int a = ai_player[g];
     const BB o_st = (a == 1) ? white : black;
-    long long s_a = warp_pattern_score(a_st, empty, lane);
+    // line words of both colours and the per-line pattern score of A (gz_lines.cuh)
+    __shared__ uint32_t s_st[4][2][8];
+    __shared__ uint16_t s_la[4][kNumLines], s_lb[4][kNumLines];
+    __shared__ int32_t s_ls[4][kNumLines];
+    const int wi = threadIdx.x >> 5;
+    if (lane < 16) s_st[wi][lane >> 3][lane & 7] = b.stones[(lane >> 3) ^ (a == 1 ? 0 : 1)][lane & 7];
+    __syncwarp();
+    int ls_sum = 0;
+    for (int i = lane; i < kNumLines; i += 32) {
+        int r0, c0, len;
+        line_cell(i, 0, r0, c0, len);
+        uint32_t xa = line_word(s_st[wi][0], i), xb = line_word(s_st[wi][1], i);
+        int32_t v = line_score(xa, ((1u << len) - 1u) & ~(xa | xb));
+        s_la[wi][i] = (uint16_t)xa;
+        s_lb[wi][i] = (uint16_t)xb;
+        s_ls[wi][i] = v;
+        ls_sum += v;
+    }
+    const long long s_a = warp_sum_ll((long long)ls_sum);   // _pattern_score(board, A), also syncs the warp
+    __syncwarp();
     BB win_b, three_b;
     win_three_masks(o_st, empty, win_b, three_b);
+    const int n_win_b = bb_count(win_b);
     long long sc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         int p = 32 * i + lane;
-        sc[i] = ((empty.w[i] >> lane) & 1u) ? planner_score2(b, black, white, empty, a, s_a, win_b, p)
-                                            : kNoScore;
+        sc[i] = ((empty.w[i] >> lane) & 1u)
+                    ? planner_score2_lines(s_la[wi], s_lb[wi], s_ls[wi], s_a, n_win_b,
+                                           (win_b.w[i] >> lane) & 1u, b.to_move, a, b.move_count, p)
+                    : kNoScore;
         if (scores2 && (p >> 4) < 15 && (p & 15) < 15) scores2[(size_t)g * kCells + bit_to_cell(p)] = sc[i];
     }
     // stable descending top-k: k rounds of (max score, smallest position)

@@ -4,7 +4,7 @@
 // not part of libgomoku_b200.so and nothing in the product imports it.
 #include <cstring>
 
-#include "../../alphazero-gomoku_b200/csrc/gz_policy.cuh"
+#include "../../alphazero-gomoku_b200/csrc/gz_lines.cuh"
 
 using namespace gz;
 
@@ -103,6 +103,36 @@ void hs_planner_scores2(const uint8_t *cells, int to_move, int move_count, int a
     for (int i = 0; i < 225; ++i) {
         int p = cell_to_bit(i);
         scores225[i] = bb_test(e, p) ? planner_score2(b, bl, wh, e, ai, s_a, wb, p) : INT64_MIN;
+    }
+}
+
+// the same scores through the line-decomposed form the kernel uses (gz_lines.cuh)
+void hs_planner_scores2_lines(const uint8_t *cells, int to_move, int move_count, int ai,
+                              int64_t *scores225) {
+    gz_board b = from_cells(cells, to_move, move_count);
+    BB bl = bb_load(b.stones[0]), wh = bb_load(b.stones[1]);
+    BB e = bb_empty_cells(bl, wh);
+    const BB &a_st = ai == 1 ? bl : wh;
+    const BB &o_st = ai == 1 ? wh : bl;
+    uint16_t la[kNumLines], lb[kNumLines];
+    int32_t ls[kNumLines];
+    int64_t s_a = 0;
+    for (int i = 0; i < kNumLines; ++i) {
+        int r, c, len;
+        line_cell(i, 0, r, c, len);
+        la[i] = (uint16_t)line_word(a_st.w, i);
+        lb[i] = (uint16_t)line_word(o_st.w, i);
+        ls[i] = line_score(la[i], ((1u << len) - 1u) & ~(uint32_t)(la[i] | lb[i]));
+        s_a += ls[i];
+    }
+    BB wb, tb;
+    win_three_masks(o_st, e, wb, tb);
+    int nwb = bb_count(wb);
+    for (int i = 0; i < 225; ++i) {
+        int p = cell_to_bit(i);
+        scores225[i] = bb_test(e, p) ? planner_score2_lines(la, lb, ls, s_a, nwb, bb_test(wb, p), b.to_move,
+                                                            ai, b.move_count, p)
+                                     : INT64_MIN;
     }
 }
 

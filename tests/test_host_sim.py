@@ -112,10 +112,12 @@ def test_planner_scores_vs_golden():
     for i in range(len(g["cells"])):
         s2 = np.zeros(225, np.int64)
         cells = np.ascontiguousarray(g["cells"][i], np.uint8)
-        L.hs_planner_scores2(P(cells), int(g["to_move"][i]), int(g["move_count"][i]),
-                             int(g["ai_player"][i]), P(s2))
         want = g["scores"][i]
         occ = np.isnan(want)
-        assert np.all(s2[occ] == np.iinfo(np.int64).min)
-        assert np.array_equal(s2[~occ], np.round(want[~occ] * 2).astype(np.int64))
         assert np.all(want[~occ] * 2 == np.round(want[~occ] * 2))
+        # per-cell form and the line-decomposed form the kernel uses (gz_lines.cuh)
+        for fn in (L.hs_planner_scores2, L.hs_planner_scores2_lines):
+            s2[:] = 0
+            fn(P(cells), int(g["to_move"][i]), int(g["move_count"][i]), int(g["ai_player"][i]), P(s2))
+            assert np.all(s2[occ] == np.iinfo(np.int64).min)
+            assert np.array_equal(s2[~occ], np.round(want[~occ] * 2).astype(np.int64))
