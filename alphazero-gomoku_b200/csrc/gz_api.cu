@@ -106,7 +106,7 @@ extern "C" int gz_destroy(gz_handle h) {
                     e->sim.need_eval, e->sim.steps, e->sim.value, e->sim.topk, e->sim.ntop, e->act[0],
                     e->act[1], e->act[2], e->gn_logits, e->gn_policy, e->dqn_q, e->pv_logits,
                     e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
-                    e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
+                    e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->bw.dqn_w, e->bw.dqn_bias, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
     cudaStreamDestroy(e->own_stream);
@@ -182,6 +182,18 @@ static void pack_conv_bf16(std::vector<uint16_t> &out, const float *w, const flo
                         size_t o = base + ((((size_t)(tap * chunks + ch) * 8 + cgl) * cout + co) * 8 + j);
                         out[o] = f2bf((float)((double)w[((size_t)co * cin + ci) * T + tap] * scale));
                     }
+                }
+}
+// linear weight [nout][nin] -> K-chunks of 64 inputs: [chunk][8 k-groups][256 n][8 k] bf16, zero padded
+static void pack_fc_bf16(std::vector<uint16_t> &out, const float *w, int nout, int nin, int chunks) {
+    size_t base = out.size();
+    out.resize(base + (size_t)chunks * 8 * 256 * 8, 0);
+    for (int c = 0; c < chunks; ++c)
+        for (int kg = 0; kg < 8; ++kg)
+            for (int n = 0; n < nout; ++n)
+                for (int j = 0; j < 8; ++j) {
+                    int k = 64 * c + 8 * kg + j;
+                    if (k < nin) out[base + ((((size_t)c * 8 + kg) * 256 + n) * 8 + j)] = f2bf(w[(size_t)n * nin + k]);
                 }
 }
 static int upload_bytes(const void *src, size_t bytes, uint8_t **dev) {
@@ -307,6 +319,16 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         int rc = upload(pk, &d);
         if (rc) return rc;
         e->dqn = {d + o[0], d + o[1], d + o[2], d + o[3], d + o[4], d + o[5]};
+        std::vector<uint16_t> bf;
+        std::vector<float> bias(3 * 256, 0.f);
+        const float *q = dqf;
+        pack_fc_bf16(bf, q, 256, 675, 11); memcpy(&bias[0], q + 256 * 675, 256 * sizeof(float)); q += 256 * 675 + 256;
+        pack_fc_bf16(bf, q, 256, 256, 4); memcpy(&bias[256], q + 65536, 256 * sizeof(float)); q += 65536 + 256;
+        pack_fc_bf16(bf, q, 225, 256, 4); memcpy(&bias[512], q + 225 * 256, 225 * sizeof(float));
+        rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.dqn_w);
+        if (rc) return rc;
+        rc = upload_bytes(bias.data(), bias.size() * sizeof(float), reinterpret_cast<uint8_t **>(&e->bw.dqn_bias));
+        if (rc) return rc;
     }
     e->have_planner = true;
     return GZ_OK;

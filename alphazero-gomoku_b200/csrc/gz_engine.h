@@ -53,6 +53,8 @@ struct Bf16Weights {
     uint8_t *gn_l3_w[4];
     uint8_t *gn_l1_w[4];
     uint8_t *pv_blob, *gn_blob;
+    uint8_t *dqn_w;       // OpponentDQN: 19 K-chunks of [8 k-groups][256 n][8 k] bf16 (gz_nn_fc.cu)
+    float *dqn_bias;      // [3][256]
 };
 
 // Flat SoA tree storage, tree g owns slots [g*cap, (g+1)*cap); node 0 is the root.
@@ -188,6 +190,8 @@ void nn_planner_tail_from_planes(Engine &e, const uint8_t *planes, const gz_boar
                                  float *gn_logits, float *gn_policy, float *dqn_q, cudaStream_t s);
 void nn_debug_pv_layer_bf16(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s);
 void nn_debug_pv_layer_fp32(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s);
+// OpponentDQN as chained tcgen05 GEMMs (gz_nn_fc.cu)
+void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStream_t s);
 // precision dispatch
 void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
                    float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s);

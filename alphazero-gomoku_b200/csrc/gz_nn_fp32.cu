@@ -374,9 +374,7 @@ void nn_planner_tail_from_planes(Engine &e, const uint8_t *planes, const gz_boar
         w.hfc_b, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr,
         nullptr, nullptr, 0, nullptr);
     prof_end(e, s);
-    prof_begin(e, GZ_STAGE_DQN, 1, s);
-    k_dqn<<<(G + kDqnNB - 1) / kDqnNB, 256, 0, s>>>(boards, nullptr, G, e.dqn, dqn_q);
-    prof_end(e, s);
+    nn_dqn_bf16(e, boards, G, dqn_q, s);
 }
 
 void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,

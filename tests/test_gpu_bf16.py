@@ -56,7 +56,7 @@ def test_planner_nets_vs_reference(engines):
     gl, gp, q = (t.cpu().numpy() for t in b16.planner_nets_forward(_boards(b16, g["cells"])))
     # GraphNet logits are O(3) with the spread-out test weights: 2e-2 relative to their scale
     assert np.max(np.abs(gl - g["gn_logits"])) < 2e-2 * max(1.0, np.abs(g["gn_logits"]).max())
-    assert np.max(np.abs(q - g["dqn_q"])) < 1e-4            # the DQN stays fp32
+    assert np.max(np.abs(q - g["dqn_q"])) < 2e-2            # chained tcgen05 GEMMs, bf16 operands
 
 
 def test_search_trees_do_not_depend_on_precision(engines):
