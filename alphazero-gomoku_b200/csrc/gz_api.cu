@@ -184,6 +184,19 @@ static void pack_conv_bf16(std::vector<uint16_t> &out, const float *w, const flo
                     }
                 }
 }
+// input convolution [cout][3][3][3] (+ BN) -> per tap [2 channel groups][cout][8 channels] bf16 with
+// channels 0..2 = black / white / empty and the other 13 zero (FROM_BOARD mode of k_conv_umma)
+static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const float *bn, int cout) {
+    size_t base = out.size();
+    out.resize(base + (size_t)9 * 2 * cout * 8, 0);
+    for (int tap = 0; tap < 9; ++tap)
+        for (int co = 0; co < cout; ++co) {
+            double scale = bn ? (double)bn[co] / sqrt((double)bn[3 * cout + co] + 1e-5) : 1.0;
+            for (int ci = 0; ci < 3; ++ci)
+                out[base + (((size_t)tap * 2 + 0) * cout + co) * 8 + ci] =
+                    f2bf((float)((double)w[((size_t)co * 3 + ci) * 9 + tap] * scale));
+        }
+}
 // linear weight [nout][nin] -> K-chunks of 64 inputs: [chunk][8 k-groups][256 n][8 k] bf16, zero padded
 static void pack_fc_bf16(std::vector<uint16_t> &out, const float *w, int nout, int nin, int chunks) {
     size_t base = out.size();
@@ -258,9 +271,12 @@ extern "C" int gz_set_pv_weights(gz_handle h, const float *f, int64_t n) {
             pack_conv_bf16(bf, c2w, bn2, 128, 128, 3);
             q = bn2 + 512;
         }
+        size_t off0 = bf.size() * 2;
+        pack_conv0_bf16(bf, f, f + 3456 + 128, 128);
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.pv_blob);
         if (rc) return rc;
         for (int i = 0; i < 4; ++i) e->bw.pv_tower_w[i] = e->bw.pv_blob + off[i];
+        e->bw.pv_conv0_w = e->bw.pv_blob + off0;
     }
     e->have_pv = true;
     return GZ_OK;
@@ -304,9 +320,12 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
             o1[i] = bf.size() * 2;
             pack_conv_bf16(bf, q, nullptr, 64, 64, 1); q += 4096 + 64;
         }
+        size_t off0 = bf.size() * 2;
+        pack_conv0_bf16(bf, gnf, nullptr, 64);
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.gn_blob);
         if (rc) return rc;
         for (int i = 0; i < 4; ++i) { e->bw.gn_l3_w[i] = e->bw.gn_blob + o3[i]; e->bw.gn_l1_w[i] = e->bw.gn_blob + o1[i]; }
+        e->bw.gn_embed_w = e->bw.gn_blob + off0;
     }
     {
         Packer pk;

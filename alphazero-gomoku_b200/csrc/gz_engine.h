@@ -52,6 +52,7 @@ struct Bf16Weights {
     uint8_t *pv_tower_w[4];
     uint8_t *gn_l3_w[4];
     uint8_t *gn_l1_w[4];
+    uint8_t *pv_conv0_w, *gn_embed_w;   // input convolutions, [tap][2 cg][cout][8]
     uint8_t *pv_blob, *gn_blob;
     uint8_t *dqn_w;       // OpponentDQN: 19 K-chunks of [8 k-groups][256 n][8 k] bf16 (gz_nn_fc.cu)
     float *dqn_bias;      // [3][256]

@@ -26,18 +26,22 @@ namespace gz {
 template <int CIN, int COUT, int TAPS, bool RESIDENT>
 struct ConvCfg {
     static constexpr int CG = CIN / 8;                       // channel groups of the input
-    static constexpr int CHUNKS = CIN / 64;                  // 64-channel K chunks per tap
+    static constexpr int KSTEP = CIN < 64 ? CIN : 64;        // input channels per K-step
+    static constexpr int KK = KSTEP / 16;                    // UMMAs (K = 16) per K-step and M half
+    static constexpr int CHUNKS = CIN / KSTEP;               // K chunks per tap
     static constexpr int KSTEPS = TAPS * CHUNKS;
     static constexpr int SLAB_ROWS = TAPS == 9 ? 290 : 256;  // positions [-1,289) or [16,272)
     static constexpr int SLAB_BYTES = CG * SLAB_ROWS * 16;
-    static constexpr int WSTEP_BYTES = 8 * COUT * 16;        // one K-step of weights: [8 cg][COUT][8]
+    static constexpr int WSTEP_BYTES = (KSTEP / 8) * COUT * 16;   // one K-step of weights: [cg][COUT][8]
     static constexpr int NSTAGE = RESIDENT ? KSTEPS : 4;
     static constexpr int W_BYTES = NSTAGE * WSTEP_BYTES;
     static constexpr int TCOLS = 4 * COUT;                   // 2 buffers x 2 halves x COUT fp32 columns
     static constexpr int SMEM = 2 * SLAB_BYTES + W_BYTES + COUT * 4 + 256 + 128;
 };
 
-template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL>
+// FROM_BOARD: the input is the board itself (CIN = 16: channel 0 black, 1 white, 2 empty, the rest
+// zero); the producer warp writes the one-hot slab from the bitboards instead of copying planes.
+template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false>
 __global__ void __launch_bounds__(192, 1)
 k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w_packed,
             const float *__restrict__ bias, const uint8_t *__restrict__ res_planes,
@@ -67,13 +71,50 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
         ptx::fence_mbar_init();
     }
     for (int i = threadIdx.x; i < COUT; i += blockDim.x) sbias[i] = bias[i];
+    if (FROM_BOARD) {   // channel group 1 and the rows outside the board stay zero for the whole kernel
+        for (int i = threadIdx.x; i < 2 * C::SLAB_BYTES / 16; i += blockDim.x)
+            reinterpret_cast<uint4 *>(slab)[i] = make_uint4(0u, 0u, 0u, 0u);
+        ptx::fence_proxy_async();
+    }
     if (warp == 1) ptx::tmem_alloc<C::TCOLS>(tmem_slot);
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (warp == 0 && FROM_BOARD) {
+        // ================= producer: one-hot slab from the bitboards =================
+        const gz_board *boards = reinterpret_cast<const gz_board *>(in_planes);
+        if (lane == 0) {
+            ptx::mbar_expect_tx(&b_full[0], C::KSTEPS * C::WSTEP_BYTES);
+            ptx::bulk_g2s(wbuf, w_packed, C::KSTEPS * C::WSTEP_BYTES, &b_full[0]);
+        }
+        uint32_t it = 0;
+        for (int b = blockIdx.x; b < G; b += gridDim.x) {
+            if (active && !active[b]) continue;
+            const int ab = it & 1;
+            const uint32_t st = lane < 16 ? boards[b].stones[lane >> 3][lane & 7] : 0u;
+            if (lane == 0) ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+            __syncwarp();
+            uint8_t *dst = slab + ab * C::SLAB_BYTES;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {           // 256 positions [16,272), 8 per lane
+                const int pos = 16 + 32 * k + lane, p = pos - 16;
+                // bit p of black / white lives in lane (p >> 5) / 8 + (p >> 5)
+                const uint32_t wb = __shfl_sync(0xffffffffu, st, p >> 5);
+                const uint32_t ww = __shfl_sync(0xffffffffu, st, 8 + (p >> 5));
+                const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+                const uint32_t bl = (wb >> (p & 31)) & 1u, wh = (ww >> (p & 31)) & 1u;
+                const uint32_t em = valid ? 1u - (bl | wh) : 0u;
+                *reinterpret_cast<uint4 *>(dst + (pos + 1) * 16) =
+                    make_uint4(bl * 0x3F80u + wh * 0x3F800000u, em * 0x3F80u, 0u, 0u);
+            }
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&a_full[ab]);
+            ++it;
+        }
+    } else if (warp == 0) {
         // ================= producer =================
         if (lane == 0) {
             if (RESIDENT) {
@@ -123,6 +164,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                 const uint32_t acc = tmem_base + ab * 2 * COUT;
                 for (int ks = 0; ks < C::KSTEPS; ++ks) {
                     const int tap = ks / C::CHUNKS, chunk = ks - tap * C::CHUNKS;
+                    constexpr int CGS = C::KSTEP / 8;       // channel groups per K-step
                     const int rowoff = TAPS == 9 ? 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1) : 0;
                     uint32_t w_addr;
                     if (RESIDENT) {
@@ -135,8 +177,8 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            uint32_t a_addr = slab_addr + ((chunk * 8 + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h) * 16;
+                        for (int k = 0; k < C::KK; ++k) {
+                            uint32_t a_addr = slab_addr + ((chunk * CGS + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h) * 16;
                             uint32_t b_addr = w_addr + 2 * k * LBO_B;
                             ptx::umma_bf16(acc + h * COUT, ptx::make_desc(a_addr, LBO_A, 128),
                                            ptx::make_desc(b_addr, LBO_B, 128), idesc, (ks | k) != 0);
@@ -273,11 +315,11 @@ k_planes_to_nchw(const uint8_t *__restrict__ planes, int C, const uint8_t *__res
 }
 
 // ---- host side -------------------------------------------------------------------------------------
-template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL>
+template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false>
 static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const float *bias,
                         const uint8_t *res, uint8_t *out, const uint8_t *active, int G, cudaStream_t s) {
     using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
-    auto kern = k_conv_umma<CIN, COUT, TAPS, RESIDENT, RESIDUAL>;
+    auto kern = k_conv_umma<CIN, COUT, TAPS, RESIDENT, RESIDUAL, FROM_BOARD>;
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
@@ -293,7 +335,8 @@ void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1], *p2 = e.planes[2];
     prof_begin(e, GZ_STAGE_PV_CONV0, 1, s);
-    k_conv0_planes<128><<<G, 256, 0, s>>>(boards, active, e.pv.conv0.w, e.pv.conv0.b, p0);
+    launch_conv<16, 128, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.pv_conv0_w,
+                                               e.pv.conv0.b, nullptr, p0, active, G, s);
     prof_end(e, s);
     prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
     launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s);
@@ -308,7 +351,8 @@ void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *ac
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1];
     prof_begin(e, GZ_STAGE_GN_CONVS, 9, s);
-    k_conv0_planes<64><<<G, 256, 0, s>>>(boards, active, e.gn.embed.w, e.gn.embed.b, p0);
+    launch_conv<16, 64, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.gn_embed_w,
+                                              e.gn.embed.b, nullptr, p0, active, G, s);
     for (int i = 0; i < 4; ++i) {
         launch_conv<64, 64, 9, true, false>(e, p0, w.gn_l3_w[i], e.gn.l3[i].b, nullptr, p1, active, G, s);
         launch_conv<64, 64, 1, true, false>(e, p1, w.gn_l1_w[i], e.gn.l1[i].b, nullptr, p0, active, G, s);
@@ -324,7 +368,8 @@ void nn_debug_planes_to_nchw(Engine &e, int which, int C, int G, float *out, cud
 void nn_debug_pv_layer_bf16(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s) {
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1], *p2 = e.planes[2];
-    k_conv0_planes<128><<<G, 256, 0, s>>>(boards, nullptr, e.pv.conv0.w, e.pv.conv0.b, p0);
+    launch_conv<16, 128, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.pv_conv0_w,
+                                               e.pv.conv0.b, nullptr, p0, nullptr, G, s);
     int last = 0;
     if (nlayers >= 1) { launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, nullptr, G, s); last = 1; }
     if (nlayers >= 2) { launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, nullptr, G, s); last = 2; }
