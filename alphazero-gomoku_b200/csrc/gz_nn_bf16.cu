@@ -246,59 +246,6 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
     if (warp == 1) ptx::tmem_dealloc<C::TCOLS>(tmem_base);
 }
 
-// ------------------------------------------------------------------------------------------------
-// First layer (3 input planes generated from the bitboards, 3x3, folded BN, ReLU) on CUDA cores:
-// 0.6 % of the network FLOPs and its inputs are single bits, so it is a table-sum per position.
-// One CTA per board, thread = one plane position in [16,272); writes bf16 planes.
-template <int COUT>
-__global__ void __launch_bounds__(256)
-k_conv0_planes(const gz_board *__restrict__ boards, const uint8_t *__restrict__ active,
-               const float *__restrict__ w /*[27][COUT]*/, const float *__restrict__ bias,
-               uint8_t *__restrict__ out_planes) {
-    __shared__ __align__(16) float sw[27 * COUT];
-    __shared__ float sb[COUT];
-    __shared__ uint32_t sbits[2][8];
-    const int b = blockIdx.x;
-    if (active && !active[b]) return;
-    for (int i = threadIdx.x; i < 27 * COUT; i += 256) sw[i] = w[i];
-    for (int i = threadIdx.x; i < COUT; i += 256) sb[i] = bias[i];
-    if (threadIdx.x < 16) sbits[threadIdx.x >> 3][threadIdx.x & 7] = boards[b].stones[threadIdx.x >> 3][threadIdx.x & 7];
-    __syncthreads();
-    const int pos = 16 + threadIdx.x;
-    const int r = (pos >> 4) - 1, c = pos & 15;
-    const bool valid = c != 15 && r <= 14;
-    // 27 input bits: plane-major (black, white, empty) x tap (ky*3+kx), as the [ci][tap] weight order
-    uint32_t inbits = 0;
-    if (valid) {
-        for (int t = 0; t < 9; ++t) {
-            int rr = r + t / 3 - 1, cc = c + t % 3 - 1;
-            if (rr < 0 || rr > 14 || cc < 0 || cc > 14) continue;   // zero padding of the conv
-            int p = (rr << 4) | cc;
-            uint32_t bl = sbits[0][p >> 5] >> (p & 31) & 1u, wh = sbits[1][p >> 5] >> (p & 31) & 1u;
-            inbits |= bl << t | wh << (9 + t) | (1u - (bl | wh)) << (18 + t);
-        }
-    }
-    const size_t obase = kGuardBytes + (size_t)b * (COUT / 8) * kPlaneBytes + (size_t)pos * 16;
-#pragma unroll 1
-    for (int cg = 0; cg < COUT / 8; ++cg) {
-        float acc[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = sb[cg * 8 + j];
-        for (int t = 0; t < 27; ++t) {
-            if (!(inbits >> t & 1u)) continue;
-            const float4 *wp = reinterpret_cast<const float4 *>(&sw[t * COUT + cg * 8]);
-            float4 w0 = wp[0], w1 = wp[1];
-            acc[0] += w0.x; acc[1] += w0.y; acc[2] += w0.z; acc[3] += w0.w;
-            acc[4] += w1.x; acc[5] += w1.y; acc[6] += w1.z; acc[7] += w1.w;
-        }
-        uint32_t pk[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            pk[j] = valid ? ptx::pack_bf16(fmaxf(acc[2 * j], 0.f), fmaxf(acc[2 * j + 1], 0.f)) : 0u;
-        *reinterpret_cast<uint4 *>(out_planes + obase + (size_t)cg * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-    }
-}
-
 // bf16 planes -> fp32 NCHW [G][C][225] (debug / parity inspection, and the input of the fp32 heads)
 __global__ void __launch_bounds__(256)
 k_planes_to_nchw(const uint8_t *__restrict__ planes, int C, const uint8_t *__restrict__ active,
@@ -312,6 +259,196 @@ k_planes_to_nchw(const uint8_t *__restrict__ planes, int C, const uint8_t *__res
             ((size_t)b * (C / 8) + ch / 8) * kPlaneBytes + (size_t)pos * 16) + (ch & 7);
         out[(size_t)b * C * kCells + i] = __uint_as_float((uint32_t)(*p) << 16);
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// One GraphNet block (bg_planner.py:34-41: conv3x3 64->64 + ReLU, conv1x1 64->64 + ReLU) fused: the
+// 3x3 output never leaves the SM.  Per board: 72 UMMAs (3x3) -> TMEM -> bias + ReLU -> bf16 "mid"
+// tile in shared memory (the A operand of the 1x1) -> 8 UMMAs -> TMEM -> bias + ReLU -> planes.
+// Both weight sets are resident in shared memory; slabs, mid tiles and both accumulators are double
+// buffered, and the issuer runs one board ahead with the 3x3 so the tensor pipe never waits for an
+// epilogue:  MMA3(0) MMA3(1) MMA1(0) MMA3(2) MMA1(1) ...
+//   warp 0     slab producer (bulk copies)          warp 1     tcgen05.mma issuer
+//   warps 2-9  epilogues: quadrant = warp & 3, M half = (warp - 2) >> 2
+struct GnBlockCfg {
+    static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
+    static constexpr int MID_BYTES = 8 * 256 * 16;
+    static constexpr int W3_BYTES = 9 * 8 * 64 * 16, W1_BYTES = 8 * 64 * 16;
+    static constexpr int SMEM = 2 * SLAB_BYTES + 2 * MID_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256;
+};
+
+__global__ void __launch_bounds__(320, 1)
+k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
+           const float *__restrict__ bias3, const float *__restrict__ bias1, uint8_t *__restrict__ out_planes,
+           int G) {
+    using C = GnBlockCfg;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *slab = smem;
+    uint8_t *mid = slab + 2 * C::SLAB_BYTES;
+    uint8_t *sw3 = mid + 2 * C::MID_BYTES;
+    uint8_t *sw1 = sw3 + C::W3_BYTES;
+    float *sb3 = reinterpret_cast<float *>(sw1 + C::W1_BYTES);
+    float *sb1 = sb3 + 64;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sb1 + 64);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *d1_full = bars + 4, *d1_empty = bars + 6;
+    uint64_t *mid_full = bars + 8, *mid_empty = bars + 10, *d2_full = bars + 12, *d2_empty = bars + 14;
+    uint64_t *w_full = bars + 16;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 17);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&a_full[i], 1);   ptx::mbar_init(&a_empty[i], 1);
+            ptx::mbar_init(&d1_full[i], 1);  ptx::mbar_init(&d1_empty[i], 8);
+            ptx::mbar_init(&mid_full[i], 8); ptx::mbar_init(&mid_empty[i], 1);
+            ptx::mbar_init(&d2_full[i], 1);  ptx::mbar_init(&d2_empty[i], 8);
+        }
+        ptx::mbar_init(w_full, 1);
+        ptx::fence_mbar_init();
+    }
+    if (threadIdx.x < 64) sb3[threadIdx.x] = bias3[threadIdx.x];
+    else if (threadIdx.x < 128) sb1[threadIdx.x - 64] = bias1[threadIdx.x - 64];
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int n_it = blockIdx.x < G ? (G - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            ptx::mbar_expect_tx(w_full, C::W3_BYTES + C::W1_BYTES);
+            for (int t = 0; t < 9; ++t) ptx::bulk_g2s(sw3 + t * 8192, w3 + t * 8192, 8192, w_full);
+            ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
+            for (int it = 0; it < n_it; ++it) {
+                const int b = blockIdx.x + it * gridDim.x, ab = it & 1;
+                ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+                ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
+                const uint8_t *src = in_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes - 16;
+                for (int cg = 0; cg < 8; ++cg)
+                    ptx::bulk_g2s(slab + ab * C::SLAB_BYTES + cg * C::SLAB_ROWS * 16,
+                                  src + (size_t)cg * kPlaneBytes, C::SLAB_ROWS * 16, &a_full[ab]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 64);
+            constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_M = 256 * 16, LBO_B = 64 * 16;
+            ptx::mbar_wait(w_full, 0);
+            const uint32_t w3_addr = ptx::smem_u32(sw3), w1_addr = ptx::smem_u32(sw1);
+            for (int it = 0; it <= n_it; ++it) {
+                if (it < n_it) {
+                    const int ab = it & 1;
+                    const uint32_t par = (it >> 1) & 1;
+                    ptx::mbar_wait(&d1_empty[ab], par ^ 1);
+                    ptx::mbar_wait(&a_full[ab], par);
+                    ptx::tc_fence_after();
+                    const uint32_t slab_addr = ptx::smem_u32(slab + ab * C::SLAB_BYTES);
+                    const uint32_t acc = tmem_base + ab * 128;
+#pragma unroll 1
+                    for (int tap = 0; tap < 9; ++tap) {
+                        const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                ptx::umma_bf16(acc + h * 64,
+                                               ptx::make_desc(slab_addr + (2 * k * C::SLAB_ROWS + rowoff + 128 * h) * 16, LBO_A, 128),
+                                               ptx::make_desc(w3_addr + tap * 8192 + 2 * k * LBO_B, LBO_B, 128),
+                                               idesc, (tap | k) != 0);
+                    }
+                    ptx::umma_commit(&a_empty[ab]);
+                    ptx::umma_commit(&d1_full[ab]);
+                }
+                if (it > 0) {
+                    const int j = it - 1, jb = j & 1;
+                    const uint32_t par = (j >> 1) & 1;
+                    ptx::mbar_wait(&mid_full[jb], par);
+                    ptx::mbar_wait(&d2_empty[jb], par ^ 1);
+                    ptx::tc_fence_after();
+                    const uint32_t mid_addr = ptx::smem_u32(mid + jb * C::MID_BYTES);
+                    const uint32_t acc = tmem_base + 256 + jb * 128;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            ptx::umma_bf16(acc + h * 64,
+                                           ptx::make_desc(mid_addr + (2 * k * 256 + 128 * h) * 16, LBO_M, 128),
+                                           ptx::make_desc(w1_addr + 2 * k * LBO_B, LBO_B, 128), idesc, k != 0);
+                    ptx::umma_commit(&mid_empty[jb]);
+                    ptx::umma_commit(&d2_full[jb]);
+                }
+            }
+        }
+    } else {
+        const int q = warp & 3, h = (warp - 2) >> 2;
+        const int row = 128 * h + 32 * q + lane;            // tile row = plane position - 16
+        const int pos = 16 + row;
+        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 64;
+        for (int it = 0; it <= n_it; ++it) {
+            if (it < n_it) {
+                const int ab = it & 1;
+                const uint32_t par = (it >> 1) & 1;
+                ptx::mbar_wait(&d1_full[ab], par);
+                ptx::mbar_wait(&mid_empty[ab], par ^ 1);
+                ptx::tc_fence_after();
+                uint8_t *dst = mid + ab * C::MID_BYTES + row * 16;
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
+                    ptx::tmem_ld16(tlane + ab * 128 + c0, v);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + sb3[c0 + 2 * i], 0.f),
+                                               fmaxf(v[2 * i + 1] + sb3[c0 + 2 * i + 1], 0.f));
+                    *reinterpret_cast<uint4 *>(dst + (c0 / 8) * 4096) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4 *>(dst + (c0 / 8 + 1) * 4096) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+                ptx::tc_fence_before();
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
+            }
+            if (it > 0) {
+                const int j = it - 1, jb = j & 1;
+                const int b = blockIdx.x + j * gridDim.x;
+                ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
+                ptx::tc_fence_after();
+                uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
+                    ptx::tmem_ld16(tlane + 256 + jb * 128 + c0, v);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + sb1[c0 + 2 * i], 0.f),
+                                                       fmaxf(v[2 * i + 1] + sb1[c0 + 2 * i + 1], 0.f)) : 0u;
+                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, const uint8_t *w1, const float *b3,
+                            const float *b1, uint8_t *out, int G, cudaStream_t s) {
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(k_gn_block, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
+        configured = true;
+    }
+    int grid = G < e.sm_count ? G : e.sm_count;
+    k_gn_block<<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, b3, b1, out, G);
 }
 
 // ---- host side -------------------------------------------------------------------------------------
@@ -350,12 +487,12 @@ void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active
 void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s) {
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1];
-    prof_begin(e, GZ_STAGE_GN_CONVS, 9, s);
+    prof_begin(e, GZ_STAGE_GN_CONVS, 5, s);
     launch_conv<16, 64, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.gn_embed_w,
                                               e.gn.embed.b, nullptr, p0, active, G, s);
-    for (int i = 0; i < 4; ++i) {
-        launch_conv<64, 64, 9, true, false>(e, p0, w.gn_l3_w[i], e.gn.l3[i].b, nullptr, p1, active, G, s);
-        launch_conv<64, 64, 1, true, false>(e, p1, w.gn_l1_w[i], e.gn.l1[i].b, nullptr, p0, active, G, s);
+    for (int i = 0; i < 4; ++i) {   // p0 -> p1 -> p0 -> p1 -> p0
+        launch_gn_block(e, (i & 1) ? p1 : p0, w.gn_l3_w[i], w.gn_l1_w[i], e.gn.l3[i].b, e.gn.l1[i].b,
+                        (i & 1) ? p0 : p1, G, s);
     }
     prof_end(e, s);
 }
