@@ -64,6 +64,13 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
     CK(cudaGetDeviceProperties(&prop, cfg->device));
     e->sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking));
+    if (e->cfg.lanes < 0 || e->cfg.lanes > kMaxLanes) { delete e; return fail(GZ_ERR_ARG, "gz_create: lanes out of range"); }
+    for (int i = 0; i < kMaxLanes; ++i) {
+        e->lane[i] = new Engine();
+        CK(cudaStreamCreateWithFlags(&e->lane_stream[i], cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&e->lane_done[i], cudaEventDisableTiming));
+    }
+    CK(cudaEventCreateWithFlags(&e->lane_go, cudaEventDisableTiming));
     const size_t G = cfg->max_games, cap = (size_t)cfg->max_simulations + 1, N = G * cap;
     TreeArrays &t = e->tree;
     t.cap = (int32_t)cap;
@@ -109,6 +116,12 @@ extern "C" int gz_destroy(gz_handle h) {
                     e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->bw.dqn_w, e->bw.dqn_bias, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
+    for (int i = 0; i < kMaxLanes; ++i) {
+        cudaStreamDestroy(e->lane_stream[i]);
+        cudaEventDestroy(e->lane_done[i]);
+        delete e->lane[i];
+    }
+    cudaEventDestroy(e->lane_go);
     cudaStreamDestroy(e->own_stream);
     delete e;
     return GZ_OK;
@@ -563,6 +576,47 @@ extern "C" int gz_rollout(gz_handle h, const gz_board *d_boards, const uint8_t *
 }
 
 // ---- search --------------------------------------------------------------------------------------
+// View of the engine restricted to games [g0, g0 + n): every per-game pointer is offset, weights and
+// tables are shared.  Games are independent, so lanes never touch each other's data.
+static Engine *lane_view(Engine *e, int l, size_t g0) {
+    Engine *v = e->lane[l];
+    v->root = e;
+    v->cfg = e->cfg;
+    v->sm_count = e->sm_count;
+    v->have_pv = e->have_pv; v->have_planner = e->have_planner;
+    v->pv = e->pv; v->gn = e->gn; v->dqn = e->dqn; v->bw = e->bw;
+    v->log_table = e->log_table; v->tanh_table = e->tanh_table; v->n_log = e->n_log; v->n_tanh = e->n_tanh;
+    v->counters = e->counters;
+    const size_t cap = e->tree.cap, n0 = g0 * cap;
+    const TreeArrays &t = e->tree;
+    v->tree = {t.cap, t.parent + n0, t.move + n0, t.status + n0, t.nchild + n0, t.nempty + n0,
+               t.visits + n0, t.value + n0, t.bgb + n0, t.vhead + n0,
+               t.prior ? t.prior + n0 * kCells : nullptr, t.n_nodes + g0, t.root + g0, t.ai_player + g0};
+    const SimArrays &m = e->sim;
+    v->sim = {m.board + g0, m.leaf + g0, m.need_eval + g0, m.steps + g0, m.value + g0,
+              m.topk + g0 * kMaxTopK, m.ntop + g0, nullptr};
+    for (int i = 0; i < 3; ++i) {
+        v->planes[i] = e->planes[i] ? e->planes[i] + g0 * 16 * kPlaneBytes : nullptr;
+        v->act[i] = e->act[i] ? e->act[i] + g0 * 128 * kCells : nullptr;
+    }
+    v->gn_logits = e->gn_logits + g0 * kCells; v->gn_policy = e->gn_policy + g0 * kCells;
+    v->dqn_q = e->dqn_q + g0 * kCells;
+    v->pv_logits = e->pv_logits + g0 * kCells; v->pv_probs = e->pv_probs + g0 * kCells;
+    v->pv_value = e->pv_value + g0;
+    return v;
+}
+
+static void search_lane(Engine *v, const gz_board *d_boards, const uint8_t *d_ai, int G, SearchCfg c,
+                        int32_t *d_cv, double *d_cval, int32_t *d_best, cudaStream_t s) {
+    prof_begin(*v, GZ_STAGE_TREE, 1, s);
+    launch_tree_init(*v, d_boards, d_ai, G, s);
+    prof_end(*v, s);
+    if (c.eval_nodes)
+        nn_pv_forward(*v, v->sim.board, v->sim.need_eval, G, nullptr, nullptr, nullptr, v->tree.prior,
+                      v->sim.leaf, s);
+    (void)d_cv; (void)d_cval; (void)d_best;
+}
+
 static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_ai, int G,
                          const gz_search_params *p, int32_t *d_cv, double *d_cval, int32_t *d_best,
                          cudaStream_t s) {
@@ -570,25 +624,48 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     if (c.S < 1 || c.S > e->cfg.max_simulations) return fail(GZ_ERR_ARG, "gz_search: num_simulations out of range");
     if (c.eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_search: gz_set_pv_weights was not called");
     if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_search: planner weights not set");
-    prof_begin(*e, GZ_STAGE_TREE, 1, s);
-    launch_tree_init(*e, d_boards, d_ai, G, s);
-    prof_end(*e, s);
-    if (c.eval_nodes)
-        nn_pv_forward(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
-                           e->tree.prior, e->sim.leaf, s);
-    for (int sim = 0; sim < c.S; ++sim) {
-        prof_begin(*e, GZ_STAGE_TREE, 1, s);
-        launch_tree_step(*e, G, c, sim, s);
-        prof_end(*e, s);
-        if (c.eval_nodes)
-            nn_pv_forward(*e, e->sim.board, e->sim.need_eval, G, nullptr, nullptr, nullptr,
-                               e->tree.prior, e->sim.leaf, s);
-        run_playouts(e, G, c, sim, s);
+    int nl = e->cfg.lanes > 0 ? e->cfg.lanes : (G >= 4096 ? 4 : G >= 1024 ? 2 : 1);
+    if (nl > G) nl = G;
+    Engine *v[kMaxLanes];
+    cudaStream_t ls[kMaxLanes];
+    int g0[kMaxLanes + 1];
+    SearchCfg lc[kMaxLanes];
+    for (int l = 0; l <= nl; ++l) g0[l] = (int)((long long)G * l / nl);
+    if (nl > 1) CK(cudaEventRecord(e->lane_go, s));
+    for (int l = 0; l < nl; ++l) {
+        v[l] = lane_view(e, l, (size_t)g0[l]);
+        ls[l] = nl > 1 ? e->lane_stream[l] : s;
+        lc[l] = c;
+        lc[l].game_base = c.game_base + (uint32_t)g0[l];   // Philox streams keyed by the global game id
+        if (nl > 1) CK(cudaStreamWaitEvent(ls[l], e->lane_go, 0));
+        search_lane(v[l], d_boards + g0[l], d_ai + g0[l], g0[l + 1] - g0[l], lc[l], nullptr, nullptr, nullptr, ls[l]);
     }
-    prof_begin(*e, GZ_STAGE_TREE, 2, s);
-    launch_tree_step(*e, G, c, c.S, s);   // backs up the last simulation
-    launch_tree_finalize(*e, G, c, d_cv, d_cval, d_best, s);
-    prof_end(*e, s);
+    // waves are issued lane by lane so that the lanes' kernels interleave in the hardware queues
+    for (int sim = 0; sim < c.S; ++sim) {
+        for (int l = 0; l < nl; ++l) {
+            const int n = g0[l + 1] - g0[l];
+            prof_begin(*v[l], GZ_STAGE_TREE, 1, ls[l]);
+            launch_tree_step(*v[l], n, lc[l], sim, ls[l]);
+            prof_end(*v[l], ls[l]);
+            if (c.eval_nodes)
+                nn_pv_forward(*v[l], v[l]->sim.board, v[l]->sim.need_eval, n, nullptr, nullptr, nullptr,
+                              v[l]->tree.prior, v[l]->sim.leaf, ls[l]);
+            run_playouts(v[l], n, lc[l], sim, ls[l]);
+        }
+    }
+    for (int l = 0; l < nl; ++l) {
+        const int n = g0[l + 1] - g0[l];
+        prof_begin(*v[l], GZ_STAGE_TREE, 2, ls[l]);
+        launch_tree_step(*v[l], n, lc[l], c.S, ls[l]);   // backs up the last simulation
+        launch_tree_finalize(*v[l], n, lc[l], d_cv ? d_cv + (size_t)g0[l] * kCells : nullptr,
+                             d_cval ? d_cval + (size_t)g0[l] * kCells : nullptr,
+                             d_best ? d_best + g0[l] : nullptr, ls[l]);
+        prof_end(*v[l], ls[l]);
+        if (nl > 1) {
+            CK(cudaEventRecord(e->lane_done[l], ls[l]));
+            CK(cudaStreamWaitEvent(s, e->lane_done[l], 0));
+        }
+    }
     CKL();
     e->searched = true;
     return GZ_OK;
@@ -697,14 +774,16 @@ static cudaEvent_t next_event(Engine &e) {
     }
     return e.ev_pool[e.ev_used++];
 }
-void prof_begin(Engine &e, int stage, int n_launches, cudaStream_t s) {
+void prof_begin(Engine &e_, int stage, int n_launches, cudaStream_t s) {
+    Engine &e = e_.root ? *e_.root : e_;
     e.launches += n_launches;
     if (!e.profiling) return;
     e.ev_stage.push_back(stage);
     e.stage_launches[stage] += n_launches;
     cudaEventRecord(next_event(e), s);
 }
-void prof_end(Engine &e, cudaStream_t s) {
+void prof_end(Engine &e_, cudaStream_t s) {
+    Engine &e = e_.root ? *e_.root : e_;
     if (!e.profiling) return;
     cudaEventRecord(next_event(e), s);
 }

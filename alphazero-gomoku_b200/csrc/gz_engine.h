@@ -89,7 +89,15 @@ struct SimArrays {
     int64_t *scores2;     // [G][225] (only when requested)
 };
 
+constexpr int kMaxLanes = 4;
+
 struct Engine {
+    // A lane view (gz_api.cu: lane_view) is an Engine whose per-game pointers are offset to a group
+    // of games; it owns nothing and forwards profiling / launch counting to `root`.
+    Engine *root;
+    Engine *lane[kMaxLanes];
+    cudaStream_t lane_stream[kMaxLanes];
+    cudaEvent_t lane_done[kMaxLanes], lane_go;
     gz_config cfg;
     int sm_count;
     cudaStream_t own_stream;

@@ -30,7 +30,7 @@ STAGES = ["tree", "pv_conv0", "pv_tower", "pv_heads", "planner_score", "gn_convs
 
 class GzConfig(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_games", C.c_int32), ("max_simulations", C.c_int32),
-                ("precision", C.c_int32), ("store_priors", C.c_int32)]
+                ("precision", C.c_int32), ("store_priors", C.c_int32), ("lanes", C.c_int32)]
 
 
 class GzSearchParams(C.Structure):
@@ -95,7 +95,7 @@ class Engine:
     """One engine handle on one GPU; all tensors it returns live on that GPU."""
 
     def __init__(self, max_games, max_simulations, device=0, precision=0, store_priors=False,
-                 host_tables=True):
+                 host_tables=True, lanes=0):
         import torch
         self.torch = torch
         self.L = load_library()
@@ -103,7 +103,7 @@ class Engine:
             raise EngineError("no CUDA device: the B200 engine has no CPU path")
         self.device = torch.device("cuda", device)
         self.max_games, self.max_simulations = int(max_games), int(max_simulations)
-        cfg = GzConfig(device, self.max_games, self.max_simulations, precision, int(store_priors))
+        cfg = GzConfig(device, self.max_games, self.max_simulations, precision, int(store_priors), int(lanes))
         self.h = C.c_void_p()
         self._ck(self.L.gz_create(C.byref(cfg), C.byref(self.h)))
         if host_tables:

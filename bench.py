@@ -193,7 +193,7 @@ def run_engine(args):
     torch.cuda.set_device(local)
     G, S = args.games, PRESET["sims"]
     eng = engine.Engine(max_games=G, max_simulations=S, device=local, store_priors=True,
-                        precision=1 if args.precision == "bf16" else 0)
+                        precision=1 if args.precision == "bf16" else 0, lanes=args.lanes)
     pv, gn, dq = synthetic_weights()
     eng.set_pv_weights(pv)
     eng.set_planner_weights(gn, dq)
@@ -306,6 +306,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--games", type=int, default=4096)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--lanes", type=int, default=0,
+                    help="independent game groups advanced on separate CUDA streams (0 = engine default)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
                     help="network arithmetic: bf16 tcgen05 (timed mode) or fp32 FFMA (parity mode)")
     args = ap.parse_args()

@@ -55,6 +55,10 @@ typedef struct {
     int32_t precision;       /* 0 = fp32 FFMA networks (parity mode, 1e-4),
                                 1 = bf16 tcgen05 networks (throughput mode, 2e-2) */
     int32_t store_priors;    /* keep MCTSNode.prior_prob per node (ai_agent.py:523,564-582) */
+    int32_t lanes;           /* gz_search splits its G games into this many independent groups, each
+                                advanced on its own CUDA stream so that one group's integer kernels
+                                overlap another's tensor kernels; 0 = default (4 when G >= 4096, 2 when G >= 1024).
+                                Results do not depend on it (games are independent). */
 } gz_config;
 
 /* Mirrors AlphaZeroGomokuAI.params + ctor arguments (ai_agent.py:29-31,65-92) and

@@ -33,7 +33,7 @@ def test_exports_match_header(lib):
 def test_struct_sizes_and_counts(lib):
     import engine
     import oracle as orc
-    assert C.sizeof(engine.GzSearchParams) == 64 and C.sizeof(engine.GzConfig) == 20
+    assert C.sizeof(engine.GzSearchParams) == 64 and C.sizeof(engine.GzConfig) == 24
     assert lib.gz_pv_param_count() == orc.lib().gzo_pv_param_count() == 711591 + 5 * 256
     assert lib.gz_graphnet_param_count() == 267749 and lib.gz_dqn_param_count() == 296673
 
@@ -43,7 +43,7 @@ def test_no_device_fails_loudly(lib):
     if torch.cuda.is_available():
         pytest.skip("a GPU is present")
     import engine
-    cfg = engine.GzConfig(0, 4, 8, 0, 0)
+    cfg = engine.GzConfig(0, 4, 8, 0, 0, 0)
     h = C.c_void_p()
     assert lib.gz_create(C.byref(cfg), C.byref(h)) == -2
     assert b"no CPU path" in lib.gz_last_error()
