@@ -37,7 +37,7 @@ class AlphaZeroGomokuAI:
 
     def __init__(self, player, difficulty="medium", model_path=None, device=None, beta=0.2,
                  planner_steps=5, time_limit=5.0, time_reward_factor=0.1, deterministic=False,
-                 seed=None):
+                 seed=None, precision="f32"):
         self.player = player
         self.difficulty = difficulty
         self.name = "AlphaZero_%s" % difficulty
@@ -60,6 +60,9 @@ class AlphaZeroGomokuAI:
         self.games_played = 0
         self._last_decision_time = None
         # engine-side extensions (not in the reference): deterministic mode and a Philox seed
+        # precision of the networks inside the engine: "f32" (FFMA, 1e-4 against torch) or "bf16"
+        # (tcgen05 tensor cores, 2e-2): the throughput mode for batched self-play
+        self.precision = precision
         self.deterministic = bool(deterministic)
         self.seed = random.getrandbits(63) if seed is None else int(seed)
         self._engine = None
@@ -74,7 +77,8 @@ class AlphaZeroGomokuAI:
                 e.close()
             cap_g = max(n_games, 1)
             e = _engine.Engine(max_games=cap_g, max_simulations=max(sims, 8),
-                               device=self.device.index or 0)
+                               device=self.device.index or 0,
+                               precision=1 if self.precision == "bf16" else 0)
             self._engine, self._packed = e, (None, None)
             self.knowledge_search._engine = e
         pv_v = weights_version(self.model.model)

@@ -102,6 +102,8 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
     return GZ_OK;
 }
 
+static void sp_free(Engine *e);
+
 extern "C" int gz_destroy(gz_handle h) {
     if (!h) return GZ_OK;
     Engine *e = reinterpret_cast<Engine *>(h);
@@ -115,6 +117,7 @@ extern "C" int gz_destroy(gz_handle h) {
                     e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
                     e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->bw.dqn_w, e->bw.dqn_bias, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
+    sp_free(e);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
     for (int i = 0; i < kMaxLanes; ++i) {
         cudaStreamDestroy(e->lane_stream[i]);
@@ -708,6 +711,113 @@ extern "C" int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t
     if (h_cval) CK(cudaMemcpyAsync(h_cval, e->io_cval, sizeof(double) * G * kCells, cudaMemcpyDeviceToHost, s));
     if (h_best) CK(cudaMemcpyAsync(h_best, e->io_best, sizeof(int32_t) * G, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    return GZ_OK;
+}
+
+// ---- self-play -----------------------------------------------------------------------------------
+static void sp_free(Engine *e) {
+    void *ptrs[] = {e->sp.boards, e->sp.ai, e->sp.best, e->sp.game_id, e->sp.generation, e->sp.staging,
+                    e->sp.out, e->sp.ctr};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    e->sp = SelfPlayArrays();
+    e->sp_alloc_games = e->sp_alloc_out = 0;
+}
+
+extern "C" int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration,
+                                 int64_t replay_capacity, void *stream) {
+    Engine *e = eng(h);
+    int rc = check_batch(e, G, "gz_selfplay_begin");
+    if (rc) return rc;
+    if (!p) return fail(GZ_ERR_ARG, "gz_selfplay_begin: null params");
+    if (p->num_simulations < 1 || p->num_simulations > e->cfg.max_simulations)
+        return fail(GZ_ERR_ARG, "gz_selfplay_begin: num_simulations out of range");
+    if (p->eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_selfplay_begin: gz_set_pv_weights was not called");
+    if (p->planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_selfplay_begin: planner weights not set");
+    long long cap = replay_capacity > 0 ? replay_capacity : 256ll * G;
+    if (cap < kMaxPlies) cap = kMaxPlies;
+    if (e->sp_alloc_games < G || e->sp_alloc_out < cap) {
+        CK(cudaDeviceSynchronize());
+        sp_free(e);
+        CK(dalloc(&e->sp.boards, (size_t)G)); CK(dalloc(&e->sp.ai, (size_t)G)); CK(dalloc(&e->sp.best, (size_t)G));
+        CK(dalloc(&e->sp.game_id, (size_t)G)); CK(dalloc(&e->sp.generation, (size_t)G));
+        CK(dalloc(&e->sp.staging, (size_t)G * kMaxPlies)); CK(dalloc(&e->sp.out, (size_t)cap));
+        CK(dalloc(&e->sp.ctr, (size_t)SP_NCTR));
+        e->sp_alloc_games = G; e->sp_alloc_out = cap;
+    }
+    e->sp.out_cap = cap;
+    cudaStream_t s = strm(stream);
+    CK(cudaMemsetAsync(e->sp.ctr, 0, SP_NCTR * sizeof(unsigned long long), s));
+    e->sp_params = *p;
+    e->sp_cfg.seed_lo = (uint32_t)(p->seed & 0xFFFFFFFFull);
+    e->sp_cfg.seed_hi = (uint32_t)(p->seed >> 32);
+    e->sp_cfg.id_base = p->game_base;
+    e->sp_cfg.id_stride = 1u << 20;   // id = game_base + slot + generation * 2^20 (see gomoku_b200.h)
+    e->sp_cfg.deterministic = p->deterministic;
+    e->sp_cfg.exploration = exploration;
+    e->sp_G = G;
+    e->sp_steps = 0;
+    launch_sp_begin(e->sp, G, e->sp_cfg, s);
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_selfplay_step(gz_handle h, void *stream) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_selfplay_step: null handle");
+    if (e->sp_G < 1) return fail(GZ_ERR_STATE, "gz_selfplay_step: gz_selfplay_begin was not called");
+    CK(cudaSetDevice(e->cfg.device));
+    cudaStream_t s = strm(stream);
+    gz_search_params p = e->sp_params;
+    // a fresh Philox key per ply: rollouts of different plies of a game are independent
+    p.seed = e->sp_params.seed + 0x9E3779B97F4A7C15ull * (uint64_t)(e->sp_steps + 1);
+    int rc = search_device(e, e->sp.boards, e->sp.ai, e->sp_G, &p, nullptr, nullptr, e->sp.best, s);
+    if (rc) return rc;
+    launch_sp_apply(e->sp, e->sp_G, e->sp_cfg, s);
+    e->launches += 1;
+    e->sp_steps += 1;
+    CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_selfplay_drain(gz_handle h, gz_replay_record *d_out, int64_t cap, int64_t *h_n, void *stream) {
+    Engine *e = eng(h);
+    if (!e || !h_n) return fail(GZ_ERR_ARG, "gz_selfplay_drain: null argument");
+    if (e->sp_G < 1) return fail(GZ_ERR_STATE, "gz_selfplay_drain: gz_selfplay_begin was not called");
+    CK(cudaSetDevice(e->cfg.device));
+    cudaStream_t s = strm(stream);
+    unsigned long long n = 0;
+    CK(cudaMemcpyAsync(&n, e->sp.ctr + SP_CURSOR, sizeof n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    *h_n = (int64_t)n;
+    if (n == 0) return GZ_OK;
+    if (!d_out || cap < (int64_t)n) return fail(GZ_ERR_ARG, "gz_selfplay_drain: output buffer too small (see *h_n)");
+    CK(cudaMemcpyAsync(d_out, e->sp.out, (size_t)n * sizeof(gz_replay_record), cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemsetAsync(e->sp.ctr + SP_CURSOR, 0, sizeof(unsigned long long), s));
+    return GZ_OK;
+}
+
+extern "C" int gz_selfplay_boards(gz_handle h, gz_board *d_out, void *stream) {
+    Engine *e = eng(h);
+    if (!e || !d_out) return fail(GZ_ERR_ARG, "gz_selfplay_boards: null argument");
+    if (e->sp_G < 1) return fail(GZ_ERR_STATE, "gz_selfplay_boards: gz_selfplay_begin was not called");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaMemcpyAsync(d_out, e->sp.boards, sizeof(gz_board) * e->sp_G, cudaMemcpyDeviceToDevice, strm(stream)));
+    return GZ_OK;
+}
+
+extern "C" int gz_selfplay_get_stats(gz_handle h, gz_selfplay_stats *out) {
+    Engine *e = eng(h);
+    if (!e || !out) return fail(GZ_ERR_ARG, "gz_selfplay_get_stats: null argument");
+    if (e->sp_G < 1) return fail(GZ_ERR_STATE, "gz_selfplay_get_stats: gz_selfplay_begin was not called");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    unsigned long long c[SP_NCTR];
+    CK(cudaMemcpy(c, e->sp.ctr, sizeof c, cudaMemcpyDeviceToHost));
+    out->games_finished = (int64_t)c[SP_GAMES]; out->plies_played = (int64_t)c[SP_PLIES];
+    out->black_wins = (int64_t)c[SP_BLACK]; out->white_wins = (int64_t)c[SP_WHITE];
+    out->draws = (int64_t)c[SP_DRAWS]; out->records_ready = (int64_t)c[SP_CURSOR];
+    out->records_dropped = (int64_t)c[SP_DROPPED]; out->steps = e->sp_steps;
     return GZ_OK;
 }
 

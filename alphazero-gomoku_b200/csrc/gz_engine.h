@@ -91,6 +91,26 @@ struct SimArrays {
 
 constexpr int kMaxLanes = 4;
 
+// ---- self-play state (gz_kernels_selfplay.cu) ---------------------------------------------------
+constexpr int kMaxPlies = 200;     // a game ends at the 200th stone at the latest (gomoku_board.py:106)
+enum { SP_CURSOR = 0, SP_GAMES, SP_PLIES, SP_BLACK, SP_WHITE, SP_DRAWS, SP_DROPPED, SP_NCTR = 8 };
+struct SelfPlayArrays {
+    gz_board *boards;            // [G] current positions
+    uint8_t *ai;                 // [G] side to move = the searching AI's colour
+    int32_t *best;               // [G] answer of the last search
+    uint32_t *game_id;           // [G]
+    uint32_t *generation;        // [G] games this slot has finished
+    gz_replay_record *staging;   // [G][kMaxPlies] plies of the game in progress
+    gz_replay_record *out;       // [out_cap] finished games, labelled
+    long long out_cap;
+    unsigned long long *ctr;     // [SP_NCTR]
+};
+struct SelfPlayCfg {
+    uint32_t seed_lo, seed_hi, id_base, id_stride;
+    int32_t deterministic;
+    double exploration;
+};
+
 struct Engine {
     // A lane view (gz_api.cu: lane_view) is an Engine whose per-game pointers are offset to a group
     // of games; it owns nothing and forwards profiling / launch counting to `root`.
@@ -98,6 +118,11 @@ struct Engine {
     Engine *lane[kMaxLanes];
     cudaStream_t lane_stream[kMaxLanes];
     cudaEvent_t lane_done[kMaxLanes], lane_go;
+    SelfPlayArrays sp;
+    SelfPlayCfg sp_cfg;
+    gz_search_params sp_params;
+    int sp_G;                 // 0 = no self-play session
+    long long sp_steps, sp_alloc_games, sp_alloc_out;
     gz_config cfg;
     int sm_count;
     cudaStream_t own_stream;
@@ -177,6 +202,10 @@ void launch_tree_init(const Engine &e, const gz_board *boards, const uint8_t *ai
 void launch_tree_step(const Engine &e, int G, const SearchCfg &c, int sim, cudaStream_t s);
 void launch_tree_finalize(const Engine &e, int G, const SearchCfg &c, int32_t *child_visits,
                           double *child_value, int32_t *best_move, cudaStream_t s);
+
+// self-play kernels (gz_kernels_selfplay.cu)
+void launch_sp_begin(const SelfPlayArrays &sp, int G, const SelfPlayCfg &c, cudaStream_t s);
+void launch_sp_apply(const SelfPlayArrays &sp, int G, const SelfPlayCfg &c, cudaStream_t s);
 
 // networks, fp32 path (gz_nn_fp32.cu)
 void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active, int G,

@@ -22,6 +22,7 @@ EXPORTS = [
     "gz_board_ops", "gz_pv_forward", "gz_planner_nets_forward", "gz_planner_move",
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
     "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_get_stage_times", "gz_debug_pv_layer",
+    "gz_selfplay_begin", "gz_selfplay_step", "gz_selfplay_drain", "gz_selfplay_boards", "gz_selfplay_get_stats",
 ]
 
 STAGES = ["tree", "pv_conv0", "pv_tower", "pv_heads", "planner_score", "gn_convs", "gn_head", "dqn",
@@ -45,7 +46,16 @@ class GzCounters(C.Structure):
                                           "rollout_steps", "terminal_leaves", "kernel_launches")]
 
 
+class GzSelfplayStats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("games_finished", "plies_played", "black_wins", "white_wins", "draws",
+                                          "records_ready", "records_dropped", "steps")]
+
+
 BOARD_BYTES = 80
+# gz_replay_record (include/gomoku_b200.h): 72 bytes
+REPLAY_DTYPE = np.dtype([("stones", "<u4", (2, 8)), ("move", "u1"), ("mover", "u1"), ("outcome", "i1"),
+                         ("ply", "u1"), ("game_id", "<u4")])
+assert REPLAY_DTYPE.itemsize == 72
 
 
 class EngineError(RuntimeError):
@@ -277,6 +287,34 @@ class Engine:
         self._ck(self.L.gz_search_host(self.h, P(cells), P(tm), P(mc), P(ai), G, C.byref(params),
                                        P(cv), P(cval), P(best)))
         return cv, cval, best
+
+    # ---- self-play
+    def selfplay_begin(self, n_games, params, exploration, replay_capacity=0):
+        self._sp_games = int(n_games)
+        self._ck(self.L.gz_selfplay_begin(self.h, int(n_games), C.byref(params), C.c_double(exploration),
+                                          C.c_int64(replay_capacity), self._stream()))
+
+    def selfplay_step(self):
+        self._ck(self.L.gz_selfplay_step(self.h, self._stream()))
+
+    def selfplay_stats(self):
+        st = GzSelfplayStats()
+        self._ck(self.L.gz_selfplay_get_stats(self.h, C.byref(st)))
+        return {n: getattr(st, n) for n, _ in GzSelfplayStats._fields_}
+
+    def selfplay_drain(self):
+        """Finished-game records as a uint8 device tensor [n, 72] (view with REPLAY_DTYPE on the host)."""
+        t = self.torch
+        n = C.c_int64()
+        st = self.selfplay_stats()
+        out = t.empty((max(st["records_ready"], 1), REPLAY_DTYPE.itemsize), dtype=t.uint8, device=self.device)
+        self._ck(self.L.gz_selfplay_drain(self.h, _ptr(out), C.c_int64(out.shape[0]), C.byref(n), self._stream()))
+        return out[:n.value]
+
+    def selfplay_boards(self):
+        out = self.torch.empty((self._sp_games, BOARD_BYTES), dtype=self.torch.uint8, device=self.device)
+        self._ck(self.L.gz_selfplay_boards(self.h, _ptr(out), self._stream()))
+        return out
 
     def get_tree(self, g):
         cap = self.max_simulations + 1

@@ -198,6 +198,47 @@ int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t *h_to_move
 int gz_get_tree(gz_handle h, int32_t g, int32_t cap, int32_t *h_parent, int32_t *h_move,
                 int32_t *h_visits, double *h_value, int32_t *n_nodes);
 
+/* ---- self-play (training.py:141-218 play_one_game, :77-97 SimpleReplay) ---------------------------------- */
+/* G games are played concurrently on the device, one ply of every game per gz_selfplay_step: the
+ * position is searched (gz_search with ai_player = the side to move, as play_one_game alternates
+ * ai_black / ai_white), with probability `exploration` the searched move is replaced by a uniform random
+ * legal move (ai_agent.py:128-129), the move is played, and the ply is recorded BEFORE the move like
+ * SimpleReplay.add.  The first six plies of a game come from the opening book (ai_agent.py:138-166:
+ * (7,7), then a random free cell of the centre 3x3, else of the centre 5x5) and are played at once when
+ * a game starts, so every step searches G live positions.  When a game ends its plies are labelled
+ * (+1 mover won, -1 mover lost, 0 draw; training.py:89-94), appended to the replay buffer, and the slot
+ * starts a new game.  The wall-clock time-outs of play_one_game do not exist here. */
+typedef struct {
+    uint32_t stones[2][8]; /* position before the move, gz_board bit layout ([0] black, [1] white):
+                              the reference stores 2700 bytes of float planes instead (training.py:84) */
+    uint8_t move;          /* row*15 + col */
+    uint8_t mover;         /* 1 black, 2 white */
+    int8_t outcome;        /* +1 / -1 / 0 from the mover's point of view */
+    uint8_t ply;           /* index of the ply inside its game */
+    uint32_t game_id;      /* global id: p->game_base + slot + 2^20 * (games this slot finished before) */
+} gz_replay_record;        /* 72 bytes */
+
+typedef struct {
+    int64_t games_finished, plies_played, black_wins, white_wins, draws;
+    int64_t records_ready;   /* records waiting in the replay buffer */
+    int64_t records_dropped; /* records lost because the buffer was full (drain more often) */
+    int64_t steps;           /* gz_selfplay_step calls since gz_selfplay_begin */
+} gz_selfplay_stats;
+
+/* Starts G (<= max_games) fresh games.  `p` as for gz_search (num_simulations <= max_simulations);
+ * p->seed keys every random choice, p->game_base is the id of this handle's first game (rank * G on a
+ * multi-GPU run, so ids and random streams are global).  Replay capacity: replay_capacity records
+ * (0 = 256 per game). */
+int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration,
+                      int64_t replay_capacity, void *stream);
+/* One ply of every game. */
+int gz_selfplay_step(gz_handle h, void *stream);
+/* Moves up to `cap` finished-game records to d_out (device) and frees their space; *h_n = count. */
+int gz_selfplay_drain(gz_handle h, gz_replay_record *d_out, int64_t cap, int64_t *h_n, void *stream);
+/* Current boards of the G games (device, for inspection) and the counters. */
+int gz_selfplay_boards(gz_handle h, gz_board *d_out, void *stream);
+int gz_selfplay_get_stats(gz_handle h, gz_selfplay_stats *out);
+
 /* ---- stage timing ---------------------------------------------------------------------------------- */
 /* CUDA-event timing of the engine's kernel groups on the launching stream.  When enabled, every
  * group of launches inside gz_search / gz_rollout / gz_pv_forward / ... is bracketed by two events;
