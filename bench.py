@@ -298,6 +298,88 @@ def run_engine(args):
         dist.destroy_process_group()
 
 
+def selfplay_session(eng, G, rank, seed=2026):
+    import engine
+    p = engine.make_params(PRESET["sims"], PRESET["c_puct"], beta=PRESET["beta"],
+                           planner_steps=PRESET["planner_steps"], difficulty=PRESET["difficulty"],
+                           deterministic=False, seed=seed, game_base=rank * G)
+    eng.selfplay_begin(G, p, 0.01)        # hard preset: exploration 0.01 (ai_agent.py:84-90)
+
+
+def run_selfplay(args):
+    """Second metric of BASELINE.json: self-play games/hour, hard preset (S=200, planner_steps=5,
+    epsilon 0.01), G concurrent games per GPU with recycling, every ply one full gz_search.
+    Timed: from gz_selfplay_begin until every rank has finished --min-games games (CUDA events, max
+    over ranks); value = games finished by all ranks / that time."""
+    import torch
+    import engine
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    G = args.games
+    eng = engine.Engine(max_games=G, max_simulations=PRESET["sims"], device=local, store_priors=True,
+                        precision=1 if args.precision == "bf16" else 0, lanes=args.lanes)
+    pv, gn, dq = synthetic_weights()
+    eng.set_pv_weights(pv)
+    eng.set_planner_weights(gn, dq)
+    selfplay_session(eng, G, rank, seed=1)
+    for _ in range(args.warmup):
+        eng.selfplay_step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    eng.reset_counters()
+    selfplay_session(eng, G, rank)
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    steps = 0
+    while True:
+        eng.selfplay_step()
+        steps += 1
+        if steps % 8 == 0 or steps >= args.max_plies:
+            st = eng.selfplay_stats()
+            if st["records_ready"] > G * 128:
+                eng.selfplay_drain()
+            if st["games_finished"] >= args.min_games or steps >= args.max_plies:
+                break
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.finish()
+    st = eng.selfplay_stats()
+    cnt = eng.counters()
+    vals = torch.tensor([ms, st["games_finished"], st["plies_played"], cnt["simulations"], st["black_wins"],
+                         st["white_wins"], st["draws"]], dtype=torch.float64, device="cuda")
+    mx = vals.clone()
+    if dist is not None:
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(vals, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        t = mx[0].item() / 1e3
+        games, plies, sims = vals[1].item(), vals[2].item(), vals[3].item()
+        print(json.dumps({
+            "metric": "selfplay_games_per_hour", "value": games / t * 3600.0, "unit": "games/h", "n_gpus": world,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": mx[0].item() / steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": config_dict(G, world, {"workload": "hard preset self-play from empty boards with game "
+                                             "recycling: S=200, c_puct=1.8, beta=0.2, planner_steps=5, epsilon=0.01, "
+                                             "G=%d concurrent games per GPU" % G}),
+            "clocks": clocks, "games_finished": games, "plies_played": plies,
+            "mean_plies_per_finished_game": (plies / games) if games else None,
+            "sims_per_sec": sims / t, "plies_per_sec": plies / t,
+            "outcomes": {"black": vals[4].item(), "white": vals[5].item(), "draw": vals[6].item()},
+            "gpu_launches": cnt["kernel_launches"], "seconds": t}))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -310,7 +392,13 @@ def main():
                     help="independent game groups advanced on separate CUDA streams (0 = engine default)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
                     help="network arithmetic: bf16 tcgen05 (timed mode) or fp32 FFMA (parity mode)")
+    ap.add_argument("--mode", default="search", choices=["search", "selfplay"],
+                    help="search: sims/s on fixed positions (the headline); selfplay: games/hour")
+    ap.add_argument("--min-games", type=int, default=4096, help="selfplay mode: games to finish per rank")
+    ap.add_argument("--max-plies", type=int, default=2000)
     args = ap.parse_args()
+    if args.mode == "selfplay" and args.impl != "reference":
+        return run_selfplay(args)
     if args.impl == "reference":
         run_reference(args)
     else:
