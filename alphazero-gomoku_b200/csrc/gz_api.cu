@@ -77,7 +77,7 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
     CK(dalloc(&t.parent, N)); CK(dalloc(&t.move, N)); CK(dalloc(&t.status, N));
     CK(dalloc(&t.nchild, N)); CK(dalloc(&t.nempty, N)); CK(dalloc(&t.visits, N));
     CK(dalloc(&t.value, N)); CK(dalloc(&t.bgb, N)); CK(dalloc(&t.vhead, N));
-    if (cfg->store_priors) CK(dalloc(&t.prior, N * kCells));
+    if (cfg->store_priors) CK(dalloc(&t.prior, N * kPolicyPitch));
     CK(dalloc(&t.n_nodes, G)); CK(dalloc(&t.root, G)); CK(dalloc(&t.ai_player, G));
     SimArrays &s = e->sim;
     CK(dalloc(&s.board, G)); CK(dalloc(&s.leaf, G)); CK(dalloc(&s.need_eval, G));
@@ -88,7 +88,8 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
     } else {
         for (int i = 0; i < 3; ++i) CK(dalloc(&e->act[i], G * 128 * kCells));
     }
-    CK(dalloc(&e->gn_logits, G * kCells)); CK(dalloc(&e->gn_policy, G * kCells));
+    CK(dalloc(&e->gn_logits, G * kCells)); CK(dalloc(&e->gn_policy, G * kPolicyPitch));
+    CK(dalloc(&e->pv_pc, G * 450)); CK(dalloc(&e->pv_vc, G * kCells)); CK(dalloc(&e->gn_pc, G * 450));
     CK(dalloc(&e->dqn_q, G * kCells));
     CK(dalloc(&e->pv_logits, G * kCells)); CK(dalloc(&e->pv_probs, G * kCells));
     CK(dalloc(&e->pv_value, G));
@@ -115,7 +116,7 @@ extern "C" int gz_destroy(gz_handle h) {
                     e->sim.need_eval, e->sim.steps, e->sim.value, e->sim.topk, e->sim.ntop, e->act[0],
                     e->act[1], e->act[2], e->gn_logits, e->gn_policy, e->dqn_q, e->pv_logits,
                     e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
-                    e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->bw.dqn_w, e->bw.dqn_bias, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
+                    e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->bw.dqn_w, e->bw.dqn_bias, e->bw.pv_head_blob, e->bw.gn_head_blob, e->pv_pc, e->pv_vc, e->gn_pc, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
     sp_free(e);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
@@ -214,15 +215,15 @@ static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const fl
         }
 }
 // linear weight [nout][nin] -> K-chunks of 64 inputs: [chunk][8 k-groups][256 n][8 k] bf16, zero padded
-static void pack_fc_bf16(std::vector<uint16_t> &out, const float *w, int nout, int nin, int chunks) {
+static void pack_fc_bf16(std::vector<uint16_t> &out, const float *w, int nout, int nin, int chunks, int npad = 256) {
     size_t base = out.size();
-    out.resize(base + (size_t)chunks * 8 * 256 * 8, 0);
+    out.resize(base + (size_t)chunks * 8 * npad * 8, 0);
     for (int c = 0; c < chunks; ++c)
         for (int kg = 0; kg < 8; ++kg)
             for (int n = 0; n < nout; ++n)
                 for (int j = 0; j < 8; ++j) {
                     int k = 64 * c + 8 * kg + j;
-                    if (k < nin) out[base + ((((size_t)c * 8 + kg) * 256 + n) * 8 + j)] = f2bf(w[(size_t)n * nin + k]);
+                    if (k < nin) out[base + ((((size_t)c * 8 + kg) * npad + n) * 8 + j)] = f2bf(w[(size_t)n * nin + k]);
                 }
 }
 static int upload_bytes(const void *src, size_t bytes, uint8_t **dev) {
@@ -294,6 +295,23 @@ extern "C" int gz_set_pv_weights(gz_handle h, const float *f, int64_t n) {
         for (int i = 0; i < 4; ++i) e->bw.pv_tower_w[i] = e->bw.pv_blob + off[i];
         e->bw.pv_conv0_w = e->bw.pv_blob + off0;
     }
+    {   // head FCs for gz_nn_fc.cu: policy 450 -> 225 (8 chunks, N 256), value 225 -> 64 (4 chunks, N 64), bias [256]
+        const float *q = f + 3456 + 128 + 512 + 2 * (2 * (147456 + 128) + 2 * 512);
+        const float *pfc_w = q + 256 + 2, *pfc_b = pfc_w + 101250;
+        const float *vfc1_w = pfc_b + 225 + 128 + 1;
+        std::vector<uint16_t> bf;
+        pack_fc_bf16(bf, pfc_w, 225, 450, 8, 256);
+        size_t off_v = bf.size() * 2;
+        pack_fc_bf16(bf, vfc1_w, 64, 225, 4, 64);
+        size_t off_b = bf.size() * 2;
+        bf.resize(bf.size() + 512, 0);
+        memcpy(reinterpret_cast<uint8_t *>(bf.data()) + off_b, pfc_b, 225 * sizeof(float));
+        rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.pv_head_blob);
+        if (rc) return rc;
+        e->bw.pv_pfc_w = e->bw.pv_head_blob;
+        e->bw.pv_vfc1_w = e->bw.pv_head_blob + off_v;
+        e->bw.pv_pfc_b = reinterpret_cast<float *>(e->bw.pv_head_blob + off_b);
+    }
     e->have_pv = true;
     return GZ_OK;
 }
@@ -342,6 +360,18 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         if (rc) return rc;
         for (int i = 0; i < 4; ++i) { e->bw.gn_l3_w[i] = e->bw.gn_blob + o3[i]; e->bw.gn_l1_w[i] = e->bw.gn_blob + o1[i]; }
         e->bw.gn_embed_w = e->bw.gn_blob + off0;
+        {   // head FC 450 -> 225 for gz_nn_fc.cu
+            const float *hfc_w = gnf + 1728 + 64 + 4 * (36864 + 64 + 4096 + 64) + 128 + 2, *hfc_b = hfc_w + 101250;
+            std::vector<uint16_t> hb;
+            pack_fc_bf16(hb, hfc_w, 225, 450, 8, 256);
+            size_t off_b = hb.size() * 2;
+            hb.resize(hb.size() + 512, 0);
+            memcpy(reinterpret_cast<uint8_t *>(hb.data()) + off_b, hfc_b, 225 * sizeof(float));
+            rc = upload_bytes(hb.data(), hb.size() * 2, &e->bw.gn_head_blob);
+            if (rc) return rc;
+            e->bw.gn_hfc_w = e->bw.gn_head_blob;
+            e->bw.gn_hfc_b = reinterpret_cast<float *>(e->bw.gn_head_blob + off_b);
+        }
     }
     {
         Packer pk;
@@ -483,8 +513,8 @@ extern "C" int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, in
     if (!d_boards) return fail(GZ_ERR_ARG, "gz_planner_nets_forward: null pointer");
     if (!e->have_planner) return fail(GZ_ERR_STATE, "gz_planner_nets_forward: planner weights not set");
     nn_planner_forward(*e, d_boards, G, d_gn_logits ? d_gn_logits : e->gn_logits,
-                            d_gn_policy ? d_gn_policy : e->gn_policy, d_dqn_q ? d_dqn_q : e->dqn_q,
-                            strm(stream));
+                       d_gn_policy ? d_gn_policy : e->gn_policy, d_gn_policy ? kCells : kPolicyPitch,
+                       d_dqn_q ? d_dqn_q : e->dqn_q, strm(stream));
     CKL();
     return GZ_OK;
 }
@@ -516,7 +546,7 @@ extern "C" int gz_planner_move(gz_handle h, const gz_board *d_boards, const uint
     cudaStream_t s = strm(stream);
     int32_t *topk = d_topk ? d_topk : e->sim.topk;
     launch_planner_score(d_boards, d_ai_player, nullptr, G, c, step, topk, e->sim.ntop, d_scores2, s);
-    nn_planner_forward(*e, d_boards, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+    nn_planner_forward(*e, d_boards, G, e->gn_logits, e->gn_policy, kPolicyPitch, e->dqn_q, s);
     launch_planner_pick(const_cast<gz_board *>(d_boards), d_ai_player, nullptr, G, c, sim, step, topk,
                         e->sim.ntop, e->gn_policy, e->dqn_q, d_composed, d_move, false, nullptr, s);
     e->launches += 2;
@@ -545,7 +575,7 @@ static void run_playouts(Engine *e, int G, const SearchCfg &c, int sim, cudaStre
         launch_planner_score(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, k, e->sim.topk,
                              e->sim.ntop, nullptr, s);
         prof_end(*e, s);
-        nn_planner_forward(*e, e->sim.board, G, e->gn_logits, e->gn_policy, e->dqn_q, s);
+        nn_planner_forward(*e, e->sim.board, G, e->gn_logits, e->gn_policy, kPolicyPitch, e->dqn_q, s);
         prof_begin(*e, GZ_STAGE_PLAN_PICK, 1, s);
         launch_planner_pick(e->sim.board, e->tree.ai_player, e->sim.steps, G, c, sim, -1, e->sim.topk,
                             e->sim.ntop, e->gn_policy, e->dqn_q, nullptr, nullptr, true, e->counters, s);
@@ -594,7 +624,7 @@ static Engine *lane_view(Engine *e, int l, size_t g0) {
     const TreeArrays &t = e->tree;
     v->tree = {t.cap, t.parent + n0, t.move + n0, t.status + n0, t.nchild + n0, t.nempty + n0,
                t.visits + n0, t.value + n0, t.bgb + n0, t.vhead + n0,
-               t.prior ? t.prior + n0 * kCells : nullptr, t.n_nodes + g0, t.root + g0, t.ai_player + g0};
+               t.prior ? t.prior + n0 * kPolicyPitch : nullptr, t.n_nodes + g0, t.root + g0, t.ai_player + g0};
     const SimArrays &m = e->sim;
     v->sim = {m.board + g0, m.leaf + g0, m.need_eval + g0, m.steps + g0, m.value + g0,
               m.topk + g0 * kMaxTopK, m.ntop + g0, nullptr};
@@ -602,7 +632,8 @@ static Engine *lane_view(Engine *e, int l, size_t g0) {
         v->planes[i] = e->planes[i] ? e->planes[i] + g0 * 16 * kPlaneBytes : nullptr;
         v->act[i] = e->act[i] ? e->act[i] + g0 * 128 * kCells : nullptr;
     }
-    v->gn_logits = e->gn_logits + g0 * kCells; v->gn_policy = e->gn_policy + g0 * kCells;
+    v->gn_logits = e->gn_logits + g0 * kCells; v->gn_policy = e->gn_policy + g0 * kPolicyPitch;
+    v->pv_pc = e->pv_pc + g0 * 450; v->pv_vc = e->pv_vc + g0 * kCells; v->gn_pc = e->gn_pc + g0 * 450;
     v->dqn_q = e->dqn_q + g0 * kCells;
     v->pv_logits = e->pv_logits + g0 * kCells; v->pv_probs = e->pv_probs + g0 * kCells;
     v->pv_value = e->pv_value + g0;

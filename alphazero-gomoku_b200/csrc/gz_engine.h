@@ -17,6 +17,8 @@ constexpr int kTanhTableMax = 4096;
 constexpr int kPlanePos = 288;
 constexpr int kPlaneBytes = kPlanePos * 16;
 constexpr int kGuardBytes = 256;
+// row pitch (floats) of the engine's internal softmax / prior rows: 225 cells padded for 16-byte stores
+constexpr int kPolicyPitch = 256;
 
 // fp32 network parameters on the device, BN folded, laid out for the FFMA kernels:
 // conv weights as [cin][tap][cout] (cout contiguous), linear weights transposed to [in][out].
@@ -54,6 +56,9 @@ struct Bf16Weights {
     uint8_t *gn_l1_w[4];
     uint8_t *pv_conv0_w, *gn_embed_w;   // input convolutions, [tap][2 cg][cout][8]
     uint8_t *pv_blob, *gn_blob;
+    uint8_t *pv_pfc_w, *pv_vfc1_w, *gn_hfc_w;   // head FCs, K-chunks of [8 k-groups][n][8 k] (gz_nn_fc.cu)
+    float *pv_pfc_b, *gn_hfc_b;                  // [256] padded biases
+    uint8_t *pv_head_blob, *gn_head_blob;
     uint8_t *dqn_w;       // OpponentDQN: 19 K-chunks of [8 k-groups][256 n][8 k] bf16 (gz_nn_fc.cu)
     float *dqn_bias;      // [3][256]
 };
@@ -70,7 +75,7 @@ struct TreeArrays {
     double *value;
     double *bgb;          // beta * tanh(pattern_score/1e4)
     float *vhead;         // value head output of the node (never read by the search, like the reference)
-    float *prior;         // optional [cap][225] renormalised priors (MCTSNode.prior_prob)
+    float *prior;         // optional [cap][kPolicyPitch] renormalised priors (MCTSNode.prior_prob)
     int32_t *n_nodes;     // per tree
     gz_board *root;       // per tree
     uint8_t *ai_player;   // per tree
@@ -140,7 +145,8 @@ struct Engine {
     SimArrays sim;
     // network activations (fp32 path): three ping-pong buffers [G][128][225]
     float *act[3];
-    float *gn_logits, *gn_policy, *dqn_q;   // [G][225] each
+    float *gn_logits, *gn_policy, *dqn_q;   // [G][225], [G][kPolicyPitch], [G][225]
+    float *pv_pc, *pv_vc, *gn_pc;           // fused head-conv outputs: [G][450], [G][225], [G][450]
     float *pv_logits, *pv_probs, *pv_value; // [G][225], [G][225], [G]
     gz_board *tmp_boards; // [G]
     uint8_t *tmp_u8;      // [G*232] host-call staging: cells, to_move, ai_player, move_count
@@ -212,7 +218,7 @@ void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active
                         float *logits, float *probs, float *value, float *prior_out,
                         const int32_t *prior_slot, cudaStream_t s);
 void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn_logits,
-                             float *gn_policy, float *dqn_q, cudaStream_t s);
+                             float *gn_policy, int policy_pitch, float *dqn_q, cudaStream_t s);
 
 // networks, bf16 tcgen05 path (gz_nn_bf16.cu)
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
@@ -220,20 +226,17 @@ void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active
                         const int32_t *prior_slot, cudaStream_t s);
 void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s);
 void nn_debug_planes_to_nchw(Engine &e, int which, int C, int G, float *out, cudaStream_t s);
-// heads reading bf16 planes, and the planner tail (GraphNet head + DQN) shared by both paths (gz_nn_fp32.cu)
-void nn_pv_heads_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards,
-                             const uint8_t *active, int G, float *logits, float *probs, float *value,
-                             float *prior_out, const int32_t *prior_slot, cudaStream_t s);
-void nn_planner_tail_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards, int G,
-                                 float *gn_logits, float *gn_policy, float *dqn_q, cudaStream_t s);
 void nn_debug_pv_layer_bf16(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s);
 void nn_debug_pv_layer_fp32(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s);
-// OpponentDQN as chained tcgen05 GEMMs (gz_nn_fc.cu)
+// heads and OpponentDQN as tcgen05 GEMMs (gz_nn_fc.cu)
+void nn_heads_bf16(Engine &e, bool pv, const gz_board *boards, const uint8_t *active, int G, float *policy,
+                   float *logits, float *probs, float *value, float *prior, const int32_t *prior_slot,
+                   cudaStream_t s);
 void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStream_t s);
 // precision dispatch
 void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
                    float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s);
 void nn_planner_forward(Engine &e, const gz_board *boards, int G, float *gn_logits, float *gn_policy,
-                        float *dqn_q, cudaStream_t s);
+                        int policy_pitch, float *dqn_q, cudaStream_t s);
 
 }  // namespace gz

@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boa
             double a = c.alpha, na = 1.0 - c.alpha;
             for (int j = 0; j < n; ++j) {
                 int idx = topk[g * kMaxTopK + j];
-                double comp = __dsub_rn(__dmul_rn(a, (double)policy[(size_t)g * kCells + idx]),
+                double comp = __dsub_rn(__dmul_rn(a, (double)policy[(size_t)g * kPolicyPitch + idx]),
                                         __dmul_rn(na, (double)q[(size_t)g * kCells + idx]));
                 if (composed) composed[g * kMaxTopK + j] = comp;
                 if (comp > best_score) { best_score = comp; best = idx; }   // strict: first maximum

@@ -36,16 +36,26 @@ struct ConvCfg {
     static constexpr int NSTAGE = RESIDENT ? KSTEPS : 4;
     static constexpr int W_BYTES = NSTAGE * WSTEP_BYTES;
     static constexpr int TCOLS = 4 * COUT;                   // 2 buffers x 2 halves x COUT fp32 columns
-    static constexpr int SMEM = 2 * SLAB_BYTES + W_BYTES + COUT * 4 + 256 + 128;
+    static constexpr int SMEM = 2 * SLAB_BYTES + W_BYTES + COUT * 4 + 256 + 128 + (3 * COUT + 4) * 4;
 };
 
 // FROM_BOARD: the input is the board itself (CIN = 16: channel 0 black, 1 white, 2 empty, the rest
 // zero); the producer warp writes the one-hot slab from the bitboards instead of copying planes.
-template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false>
+// HEADS (the last tower convolution of AlphaZeroGomokuNet): the 1x1 head convolutions 128 -> 2 (policy)
+// and 128 -> 1 (value), neither with BN nor activation (neural_network.py:149,154), are applied to the
+// fp32 epilogue values; only their outputs are written (heads.pc f32 [G][450] channel-major like the
+// flatten at :150, heads.vc f32 [G][225]) and the 128-channel planes of the last layer are not stored.
+struct HeadConv {
+    const float *pw, *pb;   // [COUT][2], [2]
+    const float *vw, *vb;   // [COUT], [1]
+    float *pc, *vc;
+};
+
+template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false, bool HEADS = false>
 __global__ void __launch_bounds__(192, 1)
 k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w_packed,
             const float *__restrict__ bias, const uint8_t *__restrict__ res_planes,
-            uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G) {
+            uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G, HeadConv heads) {
     using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *slab = smem;                                   // [2][SLAB_BYTES]
@@ -55,8 +65,14 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
     uint64_t *a_full = bars, *a_empty = bars + 2, *acc_full = bars + 4, *acc_empty = bars + 6;
     uint64_t *b_full = bars + 8, *b_empty = bars + 8 + 4;   // ring (streaming) or b_full[0] = "resident loaded"
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16 + 2);
+    float *s_hw = reinterpret_cast<float *>(bars + 32);     // HEADS: [COUT][2] policy, [COUT] value, 3 biases
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (HEADS) {
+        for (int i = threadIdx.x; i < 2 * COUT; i += blockDim.x) s_hw[i] = heads.pw[i];
+        for (int i = threadIdx.x; i < COUT; i += blockDim.x) s_hw[2 * COUT + i] = heads.vw[i];
+        if (threadIdx.x == 0) { s_hw[3 * COUT] = heads.pb[0]; s_hw[3 * COUT + 1] = heads.pb[1]; s_hw[3 * COUT + 2] = heads.vb[0]; }
+    }
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&a_full[i], 1);
@@ -209,6 +225,8 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                 const int pos = 16 + 128 * h + 32 * q + lane;
                 const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
                 const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + ab * 2 * COUT + h * COUT;
+                float hp0 = 0.f, hp1 = 0.f, hv0 = 0.f;
+                if (HEADS) { hp0 = s_hw[3 * COUT]; hp1 = s_hw[3 * COUT + 1]; hv0 = s_hw[3 * COUT + 2]; }
 #pragma unroll 1
                 for (int c0 = 0; c0 < COUT; c0 += 16) {
                     float v[16];
@@ -224,6 +242,16 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                             v[2 * i + 1] += __uint_as_float(rr[i] & 0xFFFF0000u);
                         }
                     }
+                    if (HEADS) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float x = fmaxf(v[i] + sbias[c0 + i], 0.f);
+                            hp0 = fmaf(s_hw[2 * (c0 + i)], x, hp0);
+                            hp1 = fmaf(s_hw[2 * (c0 + i) + 1], x, hp1);
+                            hv0 = fmaf(s_hw[2 * COUT + c0 + i], x, hv0);
+                        }
+                        continue;
+                    }
                     uint32_t pk[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -233,6 +261,12 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                     }
                     *reinterpret_cast<uint4 *>(out_planes + o0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4 *>(out_planes + o0 + kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+                if (HEADS && valid) {
+                    const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
+                    heads.pc[(size_t)b * 450 + cell] = hp0;
+                    heads.pc[(size_t)b * 450 + kCells + cell] = hp1;
+                    heads.vc[(size_t)b * kCells + cell] = hv0;
                 }
             }
             ptx::tc_fence_before();
@@ -274,13 +308,19 @@ struct GnBlockCfg {
     static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
     static constexpr int MID_BYTES = 8 * 256 * 16;
     static constexpr int W3_BYTES = 9 * 8 * 64 * 16, W1_BYTES = 8 * 64 * 16;
-    static constexpr int SMEM = 2 * SLAB_BYTES + 2 * MID_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256;
+    static constexpr int SMEM = 2 * SLAB_BYTES + 2 * MID_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
 };
 
+// FINAL (the last block): the head's 1x1 convolution 64 -> 2 (bg_planner.py:43,54; no activation) is
+// applied to the fp32 epilogue values and only its 450 outputs per board are written (`head_out`
+// f32 [G][450], channel-major like the flatten at bg_planner.py:55); the 64-channel planes of the
+// last layer are never stored.
+template <bool FINAL>
 __global__ void __launch_bounds__(320, 1)
 k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
            const float *__restrict__ bias3, const float *__restrict__ bias1, uint8_t *__restrict__ out_planes,
-           int G) {
+           const float *__restrict__ head_w /*[64][2]*/, const float *__restrict__ head_b /*[2]*/,
+           float *__restrict__ head_out, int G) {
     using C = GnBlockCfg;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *slab = smem;
@@ -294,8 +334,13 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     uint64_t *mid_full = bars + 8, *mid_empty = bars + 10, *d2_full = bars + 12, *d2_empty = bars + 14;
     uint64_t *w_full = bars + 16;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 17);
+    float *c_gn_head = reinterpret_cast<float *>(bars + 32);   // [64][2] head weights, then 2 biases
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (FINAL) {
+        if (threadIdx.x >= 128 && threadIdx.x < 256) c_gn_head[threadIdx.x - 128] = head_w[threadIdx.x - 128];
+        if (threadIdx.x >= 256 && threadIdx.x < 258) c_gn_head[threadIdx.x - 128] = head_b[threadIdx.x - 256];
+    }
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&a_full[i], 1);   ptx::mbar_init(&a_empty[i], 1);
@@ -416,18 +461,38 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                 const int b = blockIdx.x + j * gridDim.x;
                 ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
                 ptx::tc_fence_after();
+                if (FINAL) {
+                    float p0 = c_gn_head[128], p1 = c_gn_head[129];
+#pragma unroll
+                    for (int c0 = 0; c0 < 64; c0 += 16) {
+                        float v[16];
+                        ptx::tmem_ld16(tlane + 256 + jb * 128 + c0, v);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float x = fmaxf(v[i] + sb1[c0 + i], 0.f);
+                            p0 = fmaf(c_gn_head[2 * (c0 + i)], x, p0);
+                            p1 = fmaf(c_gn_head[2 * (c0 + i) + 1], x, p1);
+                        }
+                    }
+                    if (valid) {
+                        const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
+                        head_out[(size_t)b * 450 + cell] = p0;
+                        head_out[(size_t)b * 450 + kCells + cell] = p1;
+                    }
+                } else {
                 uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
-#pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
-                    float v[16];
-                    ptx::tmem_ld16(tlane + 256 + jb * 128 + c0, v);
-                    uint32_t pk[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + sb1[c0 + 2 * i], 0.f),
-                                                       fmaxf(v[2 * i + 1] + sb1[c0 + 2 * i + 1], 0.f)) : 0u;
-                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    #pragma unroll
+                    for (int c0 = 0; c0 < 64; c0 += 16) {
+                        float v[16];
+                        ptx::tmem_ld16(tlane + 256 + jb * 128 + c0, v);
+                        uint32_t pk[8];
+    #pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + sb1[c0 + 2 * i], 0.f),
+                                                           fmaxf(v[2 * i + 1] + sb1[c0 + 2 * i + 1], 0.f)) : 0u;
+                        *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    }
                 }
                 ptx::tc_fence_before();
                 __syncwarp();
@@ -441,29 +506,32 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
 }
 
 static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, const uint8_t *w1, const float *b3,
-                            const float *b1, uint8_t *out, int G, cudaStream_t s) {
+                            const float *b1, uint8_t *out, float *head_out, int G, cudaStream_t s) {
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(k_gn_block, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
+        cudaFuncSetAttribute(k_gn_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
+        cudaFuncSetAttribute(k_gn_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
         configured = true;
     }
     int grid = G < e.sm_count ? G : e.sm_count;
-    k_gn_block<<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, b3, b1, out, G);
+    if (head_out) k_gn_block<true><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, b3, b1, out, e.gn.hconv_w, e.gn.hconv_b, head_out, G);
+    else k_gn_block<false><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, b3, b1, out, nullptr, nullptr, nullptr, G);
 }
 
 // ---- host side -------------------------------------------------------------------------------------
-template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false>
+template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false, bool HEADS = false>
 static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const float *bias,
-                        const uint8_t *res, uint8_t *out, const uint8_t *active, int G, cudaStream_t s) {
+                        const uint8_t *res, uint8_t *out, const uint8_t *active, int G, cudaStream_t s,
+                        HeadConv heads = HeadConv()) {
     using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
-    auto kern = k_conv_umma<CIN, COUT, TAPS, RESIDENT, RESIDUAL, FROM_BOARD>;
+    auto kern = k_conv_umma<CIN, COUT, TAPS, RESIDENT, RESIDUAL, FROM_BOARD, HEADS>;
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         configured = true;
     }
     int grid = G < e.sm_count ? G : e.sm_count;
-    kern<<<grid, 192, C::SMEM, s>>>(in, w, bias, res, out, active, G);
+    kern<<<grid, 192, C::SMEM, s>>>(in, w, bias, res, out, active, G, heads);
 }
 
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
@@ -479,9 +547,10 @@ void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active
     launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s);
     launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s);
     launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s);
-    launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s);
+    HeadConv hc = {e.pv.pconv_w, e.pv.pconv_b, e.pv.vconv_w, e.pv.vconv_b, e.pv_pc, e.pv_vc};
+    launch_conv<128, 128, 9, false, true, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s, hc);
     prof_end(e, s);
-    nn_pv_heads_from_planes(e, p0, boards, active, G, logits, probs, value, prior_out, prior_slot, s);
+    nn_heads_bf16(e, true, boards, active, G, nullptr, logits, probs, value, prior_out, prior_slot, s);
 }
 
 void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s) {
@@ -492,7 +561,7 @@ void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *ac
                                               e.gn.embed.b, nullptr, p0, active, G, s);
     for (int i = 0; i < 4; ++i) {   // p0 -> p1 -> p0 -> p1 -> p0
         launch_gn_block(e, (i & 1) ? p1 : p0, w.gn_l3_w[i], w.gn_l1_w[i], e.gn.l3[i].b, e.gn.l1[i].b,
-                        (i & 1) ? p0 : p1, G, s);
+                        (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s);
     }
     prof_end(e, s);
 }

@@ -201,4 +201,278 @@ void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStr
     prof_end(e, s);
 }
 
+
+// ================================================================================================
+// Heads after the fused 1x1 head convolutions (gz_nn_bf16.cu epilogues), tile = 128 boards per CTA:
+//   policy   Linear 450 -> 225 (+ softmax over all 225 cells; neural_network.py:149-151,248-252 and
+//            bg_planner.py:43-56,247) as one tcgen05 GEMM, K = 450 padded to 512, N = 256;
+//   value    (PV) Linear 225 -> 64, ReLU, Linear 64 -> 1, tanh (neural_network.py:154-157): the
+//            first layer as a second GEMM (K 256, N 64), the 64 -> 1 dot product in the epilogue;
+//   prior    (PV) probabilities gathered over the legal cells and renormalised in float64
+//            (ai_agent.py:564-582).
+// The A operand (fp32 head-conv outputs) is split into bf16 hi + lo parts, both multiplied by the
+// same bf16 weights, so the activations keep fp32-like accuracy.  Thread = board row in the epilogue.
+namespace {
+constexpr int kHdChunksP = 8, kHdChunksV = 4;
+constexpr int kHdWBytesP = 8 * 256 * 16, kHdWBytesV = 8 * 64 * 16;
+constexpr int kSmemHead = 2 * 2 * kChunkBytesA + kWStages * kHdWBytesP + (256 + 64 + 64 + 4) * 4 + 256;
+}  // namespace
+
+struct HeadArgs {
+    const float *pc;          // [G][450] policy head conv outputs
+    const float *vc;          // [G][225] value head conv outputs (PV)
+    const gz_board *boards;   // legal mask for the prior (PV)
+    const uint8_t *active;    // optional per-board mask
+    const uint8_t *w_pol;     // 8 chunks [8 kg][256][8] bf16
+    const uint8_t *w_val;     // 4 chunks [8 kg][64][8] bf16 (PV)
+    const float *b_pol;       // [256] (225 real)
+    const float *vfc1_b, *vfc2_w, *vfc2_b;
+    float *policy;            // [G][kPolicyPitch] softmax (internal hot buffer) or nullptr
+    float *logits, *probs;    // [G][225] API outputs or nullptr
+    float *value;             // [G] or nullptr
+    float *prior;             // [node][kPolicyPitch] or nullptr
+    const int32_t *prior_slot;
+    int prior_cap;
+    float *vhead;
+    int G;
+};
+
+__device__ __forceinline__ void split_store_hi_lo(uint8_t *hi, uint8_t *lo, const float *x) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        h[j] = ptx::pack_bf16(x[2 * j], x[2 * j + 1]);                       // one cvt.rn.bf16x2.f32
+        const float r0 = x[2 * j] - __uint_as_float(h[j] << 16);
+        const float r1 = x[2 * j + 1] - __uint_as_float(h[j] & 0xFFFF0000u);
+        l[j] = ptx::pack_bf16(r0, r1);
+    }
+    *reinterpret_cast<uint4 *>(hi) = make_uint4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<uint4 *>(lo) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+template <bool PV>
+__global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *abuf = smem;                                   // [2 buffers][hi, lo][kChunkBytesA]
+    uint8_t *wbuf = abuf + 4 * kChunkBytesA;                // [kWStages][kHdWBytesP]
+    float *s_bp = reinterpret_cast<float *>(wbuf + kWStages * kHdWBytesP);
+    float *s_b1 = s_bp + 256, *s_w2 = s_b1 + 64, *s_b2 = s_w2 + 64;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(s_b2 + 4);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *b_empty = bars + 7, *d_full = bars + 10;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 12);
+    constexpr int kChunks = kHdChunksP + (PV ? kHdChunksV : 0);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&a_full[i], 128); ptx::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < kWStages; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
+        ptx::mbar_init(&d_full[0], 1); ptx::mbar_init(&d_full[1], 1);
+        ptx::fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_bp[i] = a.b_pol[i];
+    if (PV) {
+        if (threadIdx.x < 64) { s_b1[threadIdx.x] = a.vfc1_b[threadIdx.x]; s_w2[threadIdx.x] = a.vfc2_w[threadIdx.x]; }
+        if (threadIdx.x == 64) s_b2[0] = a.vfc2_b[0];
+    }
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int i = 0; i < kChunks; ++i) {
+                const int st = i % kWStages;
+                const bool pol = i < kHdChunksP;
+                const uint32_t bytes = pol ? kHdWBytesP : kHdWBytesV;
+                const uint8_t *src = pol ? a.w_pol + (size_t)i * kHdWBytesP : a.w_val + (size_t)(i - kHdChunksP) * kHdWBytesV;
+                ptx::mbar_wait(&b_empty[st], ((i / kWStages) & 1) ^ 1);
+                ptx::mbar_expect_tx(&b_full[st], bytes);
+                ptx::bulk_g2s(wbuf + st * kHdWBytesP, src, bytes / 2, &b_full[st]);
+                ptx::bulk_g2s(wbuf + st * kHdWBytesP + bytes / 2, src + bytes / 2, bytes / 2, &b_full[st]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_p = ptx::make_idesc_bf16(128, 256), idesc_v = ptx::make_idesc_bf16(128, 64);
+            constexpr uint32_t LBO_A = 128 * 16;
+            for (int i = 0; i < kChunks; ++i) {
+                const int st = i % kWStages, ab = i & 1;
+                const bool pol = i < kHdChunksP;
+                const uint32_t LBO_B = pol ? 256 * 16 : 64 * 16;
+                ptx::mbar_wait(&a_full[ab], (i >> 1) & 1);
+                ptx::mbar_wait(&b_full[st], (i / kWStages) & 1);
+                ptx::tc_fence_after();
+                const uint32_t w_addr = ptx::smem_u32(wbuf + st * kHdWBytesP);
+                const uint32_t d = tmem_base + (pol ? 0 : 256);
+                const bool first = pol ? i == 0 : i == kHdChunksP;
+#pragma unroll
+                for (int part = 0; part < 2; ++part) {
+                    const uint32_t a_addr = ptx::smem_u32(abuf + (2 * ab + part) * kChunkBytesA);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        ptx::umma_bf16(d, ptx::make_desc(a_addr + 2 * k * LBO_A, LBO_A, 128),
+                                       ptx::make_desc(w_addr + 2 * k * LBO_B, LBO_B, 128),
+                                       pol ? idesc_p : idesc_v, !(first && part == 0 && k == 0));
+                }
+                ptx::umma_commit(&a_empty[ab]);
+                ptx::umma_commit(&b_empty[st]);
+                if (i == kHdChunksP - 1) ptx::umma_commit(&d_full[0]);
+                if (PV && i == kChunks - 1) ptx::umma_commit(&d_full[1]);
+            }
+        }
+    } else {
+        const int qd = warp & 3;
+        const int m = 32 * qd + lane;
+        const int b = tile * 128 + m;
+        const bool live = b < a.G && (!a.active || a.active[b]);
+        const int bb = b < a.G ? b : a.G - 1;              // rows past the end read a valid board, write nothing
+        // ---- operand chunks: 64 inputs of every board row, fp32 -> bf16 hi + lo.  Eight lanes share a row
+        // (one k-group of 8 inputs each) so that a warp instruction touches 4 rows x 256 contiguous bytes.
+        const int wq = warp - 2;                           // rows 32*wq .. 32*wq + 31 are generated by this warp
+        for (int i = 0; i < kChunks; ++i) {
+            const int ab = i & 1;
+            const bool pol = i < kHdChunksP;
+            const int kreal = pol ? 450 : kCells;
+            const int k0 = 64 * (pol ? i : i - kHdChunksP) + 8 * (lane & 7);
+            ptx::mbar_wait(&a_empty[ab], ((i >> 1) & 1) ^ 1);
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const int row = 32 * wq + 4 * t + (lane >> 3);
+                int gb = tile * 128 + row;
+                if (gb >= a.G) gb = a.G - 1;
+                const float *src = (pol ? a.pc + (size_t)gb * 450 : a.vc + (size_t)gb * kCells) + k0;
+                float x[8];
+#pragma unroll
+                for (int j = 0; j < 8; j += 2) {
+                    if (pol) {                               // 450-float rows are 8-byte aligned
+                        float2 v2 = k0 + j < kreal ? __ldg(reinterpret_cast<const float2 *>(src + j)) : make_float2(0.f, 0.f);
+                        x[j] = v2.x; x[j + 1] = v2.y;
+                    } else {                                 // 225-float rows are only 4-byte aligned
+                        x[j] = k0 + j < kreal ? __ldg(src + j) : 0.f;
+                        x[j + 1] = k0 + j + 1 < kreal ? __ldg(src + j + 1) : 0.f;
+                    }
+                }
+                uint8_t *hi = abuf + (2 * ab) * kChunkBytesA + (lane & 7) * 128 * 16 + row * 16;
+                split_store_hi_lo(hi, hi + kChunkBytesA, x);
+            }
+            ptx::fence_proxy_async();
+            ptx::mbar_arrive(&a_full[ab]);
+        }
+        const uint32_t trow = tmem_base + ((uint32_t)(32 * qd) << 16);
+        // ---- policy: softmax over the 225 logits of this row (two passes over tensor memory: an online
+        // max / sum, then the normalised values; exp through ex2.approx like __expf)
+        ptx::mbar_wait(&d_full[0], 0);
+        ptx::tc_fence_after();
+        constexpr float kLog2e = 1.4426950408889634f;
+        float mx = -INFINITY, sum = 0.f;
+#pragma unroll 1
+        for (int c0 = 0; c0 < 240; c0 += 16) {
+            float v[16];
+            ptx::tmem_ld16(trow + c0, v);
+            float cm = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                v[j] = c0 + j < kCells ? v[j] + s_bp[c0 + j] : -INFINITY;
+                cm = fmaxf(cm, v[j]);
+            }
+            const float nm = fmaxf(mx, cm);
+            float cs = 0.f;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) cs += exp2f((v[j] - nm) * kLog2e);
+            sum = sum * exp2f((mx - nm) * kLog2e) + cs;
+            mx = nm;
+        }
+        const float inv = 1.f / sum;
+        uint32_t legal[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (PV && a.prior) {
+            BB e = bb_empty_cells(bb_load(a.boards[bb].stones[0]), bb_load(a.boards[bb].stones[1]));
+            bb_to_raster(e, legal);
+        }
+        float legal_sum = 0.f;
+        float *pol_row = a.policy ? a.policy + (size_t)bb * kPolicyPitch : nullptr;
+#pragma unroll 1
+        for (int c0 = 0; c0 < 240; c0 += 16) {
+            float v[16], pr[16];
+            ptx::tmem_ld16(trow + c0, v);
+            const uint32_t lbits = (legal[c0 >> 5] >> (c0 & 31)) & 0xFFFFu;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float lg = v[j] + s_bp[c0 + j];
+                pr[j] = c0 + j < kCells ? exp2f((lg - mx) * kLog2e) * inv : 0.f;
+                if (PV && ((lbits >> j) & 1u)) legal_sum += pr[j];
+                if (live && a.logits && c0 + j < kCells) a.logits[(size_t)b * kCells + c0 + j] = lg;
+                if (live && a.probs && c0 + j < kCells) a.probs[(size_t)b * kCells + c0 + j] = pr[j];
+            }
+            if (live && pol_row) {
+#pragma unroll
+                for (int j = 0; j < 16; j += 4)
+                    *reinterpret_cast<float4 *>(pol_row + c0 + j) = make_float4(pr[j], pr[j + 1], pr[j + 2], pr[j + 3]);
+            }
+        }
+        if (PV && a.prior) {   // warp-uniform: tcgen05.ld is .sync.aligned, only the stores are per-row
+            float *dst = a.prior + ((size_t)bb * a.prior_cap + (live ? a.prior_slot[bb] : 0)) * kPolicyPitch;
+            const float scale = legal_sum > 0.f ? inv / legal_sum : inv;   // prior = p / sum of legal p (ai_agent.py:573-582)
+#pragma unroll 1
+            for (int c0 = 0; c0 < 240; c0 += 16) {
+                float v[16], o[16];
+                ptx::tmem_ld16(trow + c0, v);
+                const uint32_t lbits = (legal[c0 >> 5] >> (c0 & 31)) & 0xFFFFu;
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    o[j] = ((lbits >> j) & 1u) ? exp2f((v[j] + s_bp[c0 + j] - mx) * kLog2e) * scale : 0.f;
+                if (live) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4)
+                        *reinterpret_cast<float4 *>(dst + c0 + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+                }
+            }
+        }
+        if (PV) {
+            ptx::mbar_wait(&d_full[1], 0);
+            ptx::tc_fence_after();
+            float sacc = 0.f;
+#pragma unroll 1
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+                ptx::tmem_ld16(trow + 256 + c0, v);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) sacc = fmaf(s_w2[c0 + j], fmaxf(v[j] + s_b1[c0 + j], 0.f), sacc);
+            }
+            const float vv = tanhf(sacc + s_b2[0]);
+            if (live) {
+                if (a.value) a.value[b] = vv;
+                if (a.vhead && a.prior_slot) a.vhead[(size_t)b * a.prior_cap + a.prior_slot[b]] = vv;
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+void nn_heads_bf16(Engine &e, bool pv, const gz_board *boards, const uint8_t *active, int G, float *policy,
+                   float *logits, float *probs, float *value, float *prior, const int32_t *prior_slot,
+                   cudaStream_t s) {
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(k_head_umma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemHead);
+        cudaFuncSetAttribute(k_head_umma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemHead);
+        configured = true;
+    }
+    HeadArgs a;
+    a.pc = pv ? e.pv_pc : e.gn_pc; a.vc = pv ? e.pv_vc : nullptr; a.boards = boards; a.active = active;
+    a.w_pol = pv ? e.bw.pv_pfc_w : e.bw.gn_hfc_w; a.w_val = pv ? e.bw.pv_vfc1_w : nullptr;
+    a.b_pol = pv ? e.bw.pv_pfc_b : e.bw.gn_hfc_b;
+    a.vfc1_b = e.pv.vfc1_b; a.vfc2_w = e.pv.vfc2_w; a.vfc2_b = e.pv.vfc2_b;
+    a.policy = policy; a.logits = logits; a.probs = probs; a.value = value; a.prior = prior;
+    a.prior_slot = prior_slot; a.prior_cap = e.tree.cap; a.vhead = prior_slot ? e.tree.vhead : nullptr; a.G = G;
+    prof_begin(e, pv ? GZ_STAGE_PV_HEADS : GZ_STAGE_GN_HEAD, 1, s);
+    if (pv) k_head_umma<true><<<(G + 127) / 128, 192, kSmemHead, s>>>(a);
+    else k_head_umma<false><<<(G + 127) / 128, 192, kSmemHead, s>>>(a);
+    prof_end(e, s);
+}
+
 }  // namespace gz

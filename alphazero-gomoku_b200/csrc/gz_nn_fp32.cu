@@ -115,7 +115,7 @@ k_heads(const float *__restrict__ x, const gz_board *__restrict__ boards,
         const float *__restrict__ vfc1_b, const float *__restrict__ vfc2_w,
         const float *__restrict__ vfc2_b, float *__restrict__ logits, float *__restrict__ probs,
         float *__restrict__ value, float *__restrict__ prior, const int32_t *__restrict__ prior_slot,
-        int prior_cap, float *__restrict__ vhead) {
+        int prior_cap, float *__restrict__ vhead, int probs_pitch) {
     __shared__ float spc[kHeadNB][450];
     __shared__ float svc[kHeadNB][kCells];
     __shared__ float slog[kHeadNB][kCells];
@@ -219,7 +219,7 @@ k_heads(const float *__restrict__ x, const gz_board *__restrict__ boards,
         float pr = ev[k] / sum;
         ev[k] = pr;
         if (logits) logits[(size_t)b * kCells + i] = slog[warp][i];
-        if (probs) probs[(size_t)b * kCells + i] = pr;
+        if (probs) probs[(size_t)b * probs_pitch + i] = pr;
         if (prior) {
             int p = cell_to_bit(i);
             uint32_t occ = (boards[b].stones[0][p >> 5] | boards[b].stones[1][p >> 5]) >> (p & 31) & 1u;
@@ -228,7 +228,7 @@ k_heads(const float *__restrict__ x, const gz_board *__restrict__ boards,
     }
     if (prior) {
         for (int o = 16; o > 0; o >>= 1) legal_sum += __shfl_xor_sync(0xffffffffu, legal_sum, o);
-        float *dst = prior + ((size_t)b * prior_cap + prior_slot[b]) * kCells;
+        float *dst = prior + ((size_t)b * prior_cap + prior_slot[b]) * kPolicyPitch;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             int i = lane + 32 * k;
@@ -316,12 +316,12 @@ void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active
     k_heads<128, true, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
         a0, boards, active, G, w.pconv_w, w.pconv_b, w.pfc_wt, w.pfc_b, w.vconv_w, w.vconv_b,
         w.vfc1_wt, w.vfc1_b, w.vfc2_w, w.vfc2_b, logits, probs, value, prior_out, prior_slot,
-        e.tree.cap, prior_slot ? e.tree.vhead : nullptr);
+        e.tree.cap, prior_slot ? e.tree.vhead : nullptr, kCells);
     prof_end(e, s);
 }
 
 void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn_logits,
-                             float *gn_policy, float *dqn_q, cudaStream_t s) {
+                             float *gn_policy, int policy_pitch, float *dqn_q, cudaStream_t s) {
     const GraphNetWeights &w = e.gn;
     float *a0 = e.act[0], *a1 = e.act[1];
     // the planner nets only see live rollout boards; finished ones are skipped via status
@@ -335,7 +335,7 @@ void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn
     prof_begin(e, GZ_STAGE_GN_HEAD, 1, s);
     k_heads<64, false, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
         a0, boards, nullptr, G, w.hconv_w, w.hconv_b, w.hfc_wt, w.hfc_b, nullptr, nullptr, nullptr,
-        nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr, nullptr, nullptr, 0, nullptr);
+        nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr, nullptr, nullptr, 0, nullptr, policy_pitch);
     prof_end(e, s);
     prof_begin(e, GZ_STAGE_DQN, 1, s);
     k_dqn<<<(G + kDqnNB - 1) / kDqnNB, 256, 0, s>>>(boards, nullptr, G, e.dqn, dqn_q);
@@ -353,30 +353,6 @@ void nn_debug_pv_layer_fp32(Engine &e, const gz_board *boards, int G, int nlayer
     cudaMemcpyAsync(out, last, sizeof(float) * (size_t)G * 128 * kCells, cudaMemcpyDeviceToDevice, s);
 }
 
-void nn_pv_heads_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards,
-                             const uint8_t *active, int G, float *logits, float *probs, float *value,
-                             float *prior_out, const int32_t *prior_slot, cudaStream_t s) {
-    const PvWeights &w = e.pv;
-    prof_begin(e, GZ_STAGE_PV_HEADS, 1, s);
-    k_heads<128, true, true><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
-        reinterpret_cast<const float *>(planes), boards, active, G, w.pconv_w, w.pconv_b, w.pfc_wt,
-        w.pfc_b, w.vconv_w, w.vconv_b, w.vfc1_wt, w.vfc1_b, w.vfc2_w, w.vfc2_b, logits, probs, value,
-        prior_out, prior_slot, e.tree.cap, prior_slot ? e.tree.vhead : nullptr);
-    prof_end(e, s);
-}
-
-void nn_planner_tail_from_planes(Engine &e, const uint8_t *planes, const gz_board *boards, int G,
-                                 float *gn_logits, float *gn_policy, float *dqn_q, cudaStream_t s) {
-    const GraphNetWeights &w = e.gn;
-    prof_begin(e, GZ_STAGE_GN_HEAD, 1, s);
-    k_heads<64, false, true><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
-        reinterpret_cast<const float *>(planes), boards, nullptr, G, w.hconv_w, w.hconv_b, w.hfc_wt,
-        w.hfc_b, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, gn_logits, gn_policy, nullptr,
-        nullptr, nullptr, 0, nullptr);
-    prof_end(e, s);
-    nn_dqn_bf16(e, boards, G, dqn_q, s);
-}
-
 void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
                    float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s) {
     if (e.cfg.precision == 1) nn_pv_forward_bf16(e, boards, active, G, logits, probs, value, prior_out, prior_slot, s);
@@ -384,12 +360,15 @@ void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int
 }
 
 void nn_planner_forward(Engine &e, const gz_board *boards, int G, float *gn_logits, float *gn_policy,
-                        float *dqn_q, cudaStream_t s) {
+                        int policy_pitch, float *dqn_q, cudaStream_t s) {
     if (e.cfg.precision == 1) {
-        nn_graphnet_convs_bf16(e, boards, nullptr, G, s);
-        nn_planner_tail_from_planes(e, e.planes[0], boards, G, gn_logits, gn_policy, dqn_q, s);
+        nn_graphnet_convs_bf16(e, boards, nullptr, G, s);      // ends with the fused head conv -> e.gn_pc
+        const bool internal = policy_pitch == kPolicyPitch;
+        nn_heads_bf16(e, false, boards, nullptr, G, internal ? gn_policy : nullptr, gn_logits,
+                      internal ? nullptr : gn_policy, nullptr, nullptr, nullptr, s);
+        nn_dqn_bf16(e, boards, G, dqn_q, s);
     } else {
-        nn_planner_forward_fp32(e, boards, G, gn_logits, gn_policy, dqn_q, s);
+        nn_planner_forward_fp32(e, boards, G, gn_logits, gn_policy, policy_pitch, dqn_q, s);
     }
 }
 
