@@ -163,8 +163,8 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer =================
-        if (lane == 0) {
+        // ================= MMA issuer (whole warp, one elected lane issues: gz_tcgen05.cuh) =================
+        {
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, COUT);
             constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = COUT * 16;
             if (RESIDENT) ptx::mbar_wait(&b_full[0], 0);
@@ -196,17 +196,17 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                         for (int k = 0; k < C::KK; ++k) {
                             uint32_t a_addr = slab_addr + ((chunk * CGS + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h) * 16;
                             uint32_t b_addr = w_addr + 2 * k * LBO_B;
-                            ptx::umma_bf16(acc + h * COUT, ptx::make_desc(a_addr, LBO_A, 128),
+                            ptx::umma_bf16_elect(acc + h * COUT, ptx::make_desc(a_addr, LBO_A, 128),
                                            ptx::make_desc(b_addr, LBO_B, 128), idesc, (ks | k) != 0);
                         }
                     }
                     if (!RESIDENT) {
-                        ptx::umma_commit(&b_empty[wstage]);
+                        ptx::umma_commit_elect(&b_empty[wstage]);
                         if (++wstage == 4) { wstage = 0; wphase ^= 1; }
                     }
                 }
-                ptx::umma_commit(&a_empty[ab]);
-                ptx::umma_commit(&acc_full[ab]);
+                ptx::umma_commit_elect(&a_empty[ab]);
+                ptx::umma_commit_elect(&acc_full[ab]);
                 ++it;
             }
         }
@@ -376,7 +376,7 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // whole warp; one elected lane issues (gz_tcgen05.cuh)
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 64);
             constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_M = 256 * 16, LBO_B = 64 * 16;
             ptx::mbar_wait(w_full, 0);
@@ -397,13 +397,13 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                         for (int h = 0; h < 2; ++h)
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                ptx::umma_bf16(acc + h * 64,
+                                ptx::umma_bf16_elect(acc + h * 64,
                                                ptx::make_desc(slab_addr + (2 * k * C::SLAB_ROWS + rowoff + 128 * h) * 16, LBO_A, 128),
                                                ptx::make_desc(w3_addr + tap * 8192 + 2 * k * LBO_B, LBO_B, 128),
                                                idesc, (tap | k) != 0);
                     }
-                    ptx::umma_commit(&a_empty[ab]);
-                    ptx::umma_commit(&d1_full[ab]);
+                    ptx::umma_commit_elect(&a_empty[ab]);
+                    ptx::umma_commit_elect(&d1_full[ab]);
                 }
                 if (it > 0) {
                     const int j = it - 1, jb = j & 1;
@@ -417,11 +417,11 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            ptx::umma_bf16(acc + h * 64,
+                            ptx::umma_bf16_elect(acc + h * 64,
                                            ptx::make_desc(mid_addr + (2 * k * 256 + 128 * h) * 16, LBO_M, 128),
                                            ptx::make_desc(w1_addr + 2 * k * LBO_B, LBO_B, 128), idesc, k != 0);
-                    ptx::umma_commit(&mid_empty[jb]);
-                    ptx::umma_commit(&d2_full[jb]);
+                    ptx::umma_commit_elect(&mid_empty[jb]);
+                    ptx::umma_commit_elect(&d2_full[jb]);
                 }
             }
         }

@@ -74,7 +74,7 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // whole warp; one elected lane issues (gz_tcgen05.cuh)
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, kFcN);
             constexpr uint32_t LBO_A = 128 * 16, LBO_B = kFcN * 16;
             int it = 0;
@@ -85,10 +85,10 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
                 const uint32_t w_addr = ptx::smem_u32(wbuf + st * kChunkBytesW);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                    ptx::umma_bf16(tmem_base + d_col, ptx::make_desc(a_addr + 2 * k * LBO_A, LBO_A, 128),
+                    ptx::umma_bf16_elect(tmem_base + d_col, ptx::make_desc(a_addr + 2 * k * LBO_A, LBO_A, 128),
                                    ptx::make_desc(w_addr + 2 * k * LBO_B, LBO_B, 128), idesc,
                                    !(first && k == 0));
-                ptx::umma_commit(&b_empty[st]);
+                ptx::umma_commit_elect(&b_empty[st]);
                 ++it;
             };
             for (int c = 0; c < kL1Chunks; ++c) {
@@ -96,17 +96,17 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
                 ptx::mbar_wait(&a_full[ab], (c >> 1) & 1);
                 ptx::tc_fence_after();
                 chunk_mmas(ptx::smem_u32(abuf + ab * kChunkBytesA), 0, c == 0);
-                ptx::umma_commit(&a_empty[ab]);
+                ptx::umma_commit_elect(&a_empty[ab]);
             }
-            ptx::umma_commit(&d_full[0]);
+            ptx::umma_commit_elect(&d_full[0]);
             ptx::mbar_wait(a2_full, 0);
             ptx::tc_fence_after();
             for (int c = 0; c < kL2Chunks; ++c) chunk_mmas(ptx::smem_u32(a2) + c * 8 * LBO_A, kFcN, c == 0);
-            ptx::umma_commit(&d_full[1]);
+            ptx::umma_commit_elect(&d_full[1]);
             ptx::mbar_wait(a2_full, 1);
             ptx::tc_fence_after();
             for (int c = 0; c < kL3Chunks; ++c) chunk_mmas(ptx::smem_u32(a2) + c * 8 * LBO_A, 0, c == 0);
-            ptx::umma_commit(&d_full[2]);
+            ptx::umma_commit_elect(&d_full[2]);
         }
     } else {
         const int qd = warp & 3;                 // TMEM lane quadrant of this warp
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // whole warp; one elected lane issues (gz_tcgen05.cuh)
             constexpr uint32_t idesc_p = ptx::make_idesc_bf16(128, 256), idesc_v = ptx::make_idesc_bf16(128, 64);
             constexpr uint32_t LBO_A = 128 * 16;
             for (int i = 0; i < kChunks; ++i) {
@@ -313,14 +313,14 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
                     const uint32_t a_addr = ptx::smem_u32(abuf + (2 * ab + part) * kChunkBytesA);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        ptx::umma_bf16(d, ptx::make_desc(a_addr + 2 * k * LBO_A, LBO_A, 128),
+                        ptx::umma_bf16_elect(d, ptx::make_desc(a_addr + 2 * k * LBO_A, LBO_A, 128),
                                        ptx::make_desc(w_addr + 2 * k * LBO_B, LBO_B, 128),
                                        pol ? idesc_p : idesc_v, !(first && part == 0 && k == 0));
                 }
-                ptx::umma_commit(&a_empty[ab]);
-                ptx::umma_commit(&b_empty[st]);
-                if (i == kHdChunksP - 1) ptx::umma_commit(&d_full[0]);
-                if (PV && i == kChunks - 1) ptx::umma_commit(&d_full[1]);
+                ptx::umma_commit_elect(&a_empty[ab]);
+                ptx::umma_commit_elect(&b_empty[st]);
+                if (i == kHdChunksP - 1) ptx::umma_commit_elect(&d_full[0]);
+                if (PV && i == kChunks - 1) ptx::umma_commit_elect(&d_full[1]);
             }
         }
     } else {

@@ -105,6 +105,33 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar) {
                  : "memory");
 }
 
+// Warp-collective forms: the WHOLE warp executes the statement and one elected lane issues.  Issuing from
+// inside an `if (lane == 0)` branch makes the compiler wrap every tcgen05.mma in R2UR moves and an
+// election loop: measured 75-94 cycles per instruction whatever N is, against max(~40, N/2) cycles with the
+// warp-uniform form below (M = 128, K = 16; scratch/umma_bench2.cu).  elect.sync with a full mask
+// returns the same lane every time, so mma and commit come from one thread as tcgen05.commit needs.
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t *bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+        "}" ::"r"(smem_u32(bar))
+        : "memory");
+}
+
 // TMEM -> registers: lane (row) = 32*(warp%4) + laneid, 16 consecutive fp32 columns
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v) {
     uint32_t r[16];
