@@ -937,6 +937,14 @@ extern "C" int gz_set_profiling(gz_handle h, int32_t on) {
     return GZ_OK;
 }
 
+extern "C" int gz_set_lanes(gz_handle h, int32_t lanes) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_set_lanes: null handle");
+    if (lanes < 0 || lanes > kMaxLanes) return fail(GZ_ERR_ARG, "gz_set_lanes: lanes out of range");
+    e->cfg.lanes = lanes;
+    return GZ_OK;
+}
+
 extern "C" int gz_get_stage_times(gz_handle h, double *h_ms, int64_t *h_launches) {
     Engine *e = eng(h);
     if (!e) return fail(GZ_ERR_ARG, "gz_get_stage_times: null handle");

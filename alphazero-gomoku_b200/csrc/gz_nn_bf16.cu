@@ -212,67 +212,87 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
         }
     } else {
         // ================= epilogue (warps 2..5) =================
+        // RESIDUAL: the skip tensor of a position (COUT x 2 B = 16 x 16 B, one per channel group) is fetched
+        // into registers a half board ahead, before the wait on the accumulator, so that its latency hides
+        // behind the MMAs instead of stalling every 16-channel step.
         const int q = warp & 3;                 // TMEM lane quadrant this warp may read
-        uint32_t it = 0;
-        for (int b = blockIdx.x; b < G; b += gridDim.x) {
-            if (active && !active[b]) continue;
-            const int ab = it & 1;
-            ptx::mbar_wait(&acc_full[ab], (it >> 1) & 1);
-            ptx::tc_fence_after();
-            const size_t obase = kGuardBytes + (size_t)b * (COUT / 8) * kPlaneBytes;
-#pragma unroll 1
-            for (int h = 0; h < 2; ++h) {
-                const int pos = 16 + 128 * h + 32 * q + lane;
-                const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
-                const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + ab * 2 * COUT + h * COUT;
-                float hp0 = 0.f, hp1 = 0.f, hv0 = 0.f;
-                if (HEADS) { hp0 = s_hw[3 * COUT]; hp1 = s_hw[3 * COUT + 1]; hv0 = s_hw[3 * COUT + 2]; }
-#pragma unroll 1
-                for (int c0 = 0; c0 < COUT; c0 += 16) {
-                    float v[16];
-                    ptx::tmem_ld16(taddr + c0, v);
-                    const size_t o0 = obase + (size_t)(c0 / 8) * kPlaneBytes + (size_t)pos * 16;
-                    if (RESIDUAL) {
-                        uint4 r0 = *reinterpret_cast<const uint4 *>(res_planes + o0);
-                        uint4 r1 = *reinterpret_cast<const uint4 *>(res_planes + o0 + kPlaneBytes);
-                        const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+        constexpr int NCG = COUT / 8;
+        uint4 res[2][RESIDUAL ? NCG : 1];
+        auto fetch_res = [&](int b, int h, uint4 *r) {
+            const uint8_t *src = res_planes + kGuardBytes + (size_t)b * NCG * kPlaneBytes +
+                                 (size_t)(16 + 128 * h + 32 * q + lane) * 16;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            v[2 * i] += __uint_as_float(rr[i] << 16);
-                            v[2 * i + 1] += __uint_as_float(rr[i] & 0xFFFF0000u);
-                        }
-                    }
-                    if (HEADS) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float x = fmaxf(v[i] + sbias[c0 + i], 0.f);
-                            hp0 = fmaf(s_hw[2 * (c0 + i)], x, hp0);
-                            hp1 = fmaf(s_hw[2 * (c0 + i) + 1], x, hp1);
-                            hv0 = fmaf(s_hw[2 * COUT + c0 + i], x, hv0);
-                        }
-                        continue;
-                    }
-                    uint32_t pk[8];
+            for (int cg = 0; cg < NCG; ++cg) r[cg] = *reinterpret_cast<const uint4 *>(src + (size_t)cg * kPlaneBytes);
+        };
+        auto half = [&](int b, int ab, int h, const uint4 *r) {
+            const size_t obase = kGuardBytes + (size_t)b * NCG * kPlaneBytes;
+            const int pos = 16 + 128 * h + 32 * q + lane;
+            const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + ab * 2 * COUT + h * COUT;
+            float hp0 = 0.f, hp1 = 0.f, hv0 = 0.f;
+            if (HEADS) { hp0 = s_hw[3 * COUT]; hp1 = s_hw[3 * COUT + 1]; hv0 = s_hw[3 * COUT + 2]; }
+#pragma unroll(RESIDUAL ? COUT / 16 : 1)
+            for (int c0 = 0; c0 < COUT; c0 += 16) {
+                float v[16];
+                ptx::tmem_ld16(taddr + c0, v);
+                const size_t o0 = obase + (size_t)(c0 / 8) * kPlaneBytes + (size_t)pos * 16;
+                if (RESIDUAL) {
+                    const uint4 r0 = r[c0 / 8], r1 = r[c0 / 8 + 1];
+                    const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        float x0 = fmaxf(v[2 * i] + sbias[c0 + 2 * i], 0.f);
-                        float x1 = fmaxf(v[2 * i + 1] + sbias[c0 + 2 * i + 1], 0.f);
-                        pk[i] = valid ? ptx::pack_bf16(x0, x1) : 0u;
+                        v[2 * i] += __uint_as_float(rr[i] << 16);
+                        v[2 * i + 1] += __uint_as_float(rr[i] & 0xFFFF0000u);
                     }
-                    *reinterpret_cast<uint4 *>(out_planes + o0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4 *>(out_planes + o0 + kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
-                if (HEADS && valid) {
-                    const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
-                    heads.pc[(size_t)b * 450 + cell] = hp0;
-                    heads.pc[(size_t)b * 450 + kCells + cell] = hp1;
-                    heads.vc[(size_t)b * kCells + cell] = hv0;
+                if (HEADS) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float x = fmaxf(v[i] + sbias[c0 + i], 0.f);
+                        hp0 = fmaf(s_hw[2 * (c0 + i)], x, hp0);
+                        hp1 = fmaf(s_hw[2 * (c0 + i) + 1], x, hp1);
+                        hv0 = fmaf(s_hw[2 * COUT + c0 + i], x, hv0);
+                    }
+                    continue;
                 }
+                uint32_t pk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float x0 = fmaxf(v[2 * i] + sbias[c0 + 2 * i], 0.f);
+                    float x1 = fmaxf(v[2 * i + 1] + sbias[c0 + 2 * i + 1], 0.f);
+                    pk[i] = valid ? ptx::pack_bf16(x0, x1) : 0u;
+                }
+                *reinterpret_cast<uint4 *>(out_planes + o0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4 *>(out_planes + o0 + kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
             }
+            if (HEADS && valid) {
+                const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
+                heads.pc[(size_t)b * 450 + cell] = hp0;
+                heads.pc[(size_t)b * 450 + kCells + cell] = hp1;
+                heads.vc[(size_t)b * kCells + cell] = hv0;
+            }
+        };
+        auto next_board = [&](int b) {
+            for (b += gridDim.x; b < G && active && !active[b]; b += gridDim.x) {}
+            return b;
+        };
+        uint32_t it = 0;
+        int b = blockIdx.x < G && active && !active[blockIdx.x] ? next_board(blockIdx.x) : blockIdx.x;
+        if (RESIDUAL && b < G) fetch_res(b, 0, res[0]);
+        while (b < G) {
+            const int ab = it & 1;
+            const int bn = next_board(b);
+            ptx::mbar_wait(&acc_full[ab], (it >> 1) & 1);
+            ptx::tc_fence_after();
+            if (RESIDUAL) fetch_res(b, 1, res[1]);
+            half(b, ab, 0, res[0]);
+            if (RESIDUAL && bn < G) fetch_res(bn, 0, res[0]);
+            half(b, ab, 1, res[1]);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[ab]);
             ++it;
+            b = bn;
         }
     }
     ptx::tc_fence_before();

@@ -21,7 +21,7 @@ EXPORTS = [
     "gz_dqn_param_count", "gz_boards_from_cells", "gz_boards_to_cells", "gz_make_moves",
     "gz_board_ops", "gz_pv_forward", "gz_planner_nets_forward", "gz_planner_move",
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
-    "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_get_stage_times", "gz_debug_pv_layer",
+    "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_set_lanes", "gz_get_stage_times", "gz_debug_pv_layer",
     "gz_selfplay_begin", "gz_selfplay_step", "gz_selfplay_drain", "gz_selfplay_boards", "gz_selfplay_get_stats",
 ]
 
@@ -334,6 +334,9 @@ class Engine:
 
     def set_profiling(self, on):
         self._ck(self.L.gz_set_profiling(self.h, int(bool(on))))
+
+    def set_lanes(self, lanes):
+        self._ck(self.L.gz_set_lanes(self.h, int(lanes)))
 
     def stage_times(self):
         """{stage: (milliseconds, launches)} accumulated since the last call (CUDA events)."""

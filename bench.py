@@ -257,6 +257,17 @@ def run_engine(args):
     h2d = G * (225 + 1 + 1 + 2)
     d2h = G * (225 * 4 + 225 * 8 + 4)
 
+    # ---- one more step with every kernel on one stream: per-launch times free of lane overlap
+    eng.set_lanes(1)
+    eng.reset_counters()
+    eng.set_profiling(True)
+    eng.stage_times()
+    eng.search(boards, ai, params(5000))
+    serial = eng.stage_times()
+    cnt_serial = eng.counters()
+    eng.set_profiling(False)
+    eng.set_lanes(args.lanes)
+
     if rank == 0:
         peaks = load_peaks()
         total_ms = sum(v[0] for v in stages.values())
@@ -273,6 +284,15 @@ def run_engine(args):
             achieved = cnt[unit] * by / (d_ms / 1e3) / 1e9
             roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
                     "frac": achieved / peaks["hbm"], "traffic": None}
+        s_ms, s_launch = serial[dom]
+        if dom in STAGE_FLOPS:
+            s_ach = cnt_serial[STAGE_FLOPS[dom][0]] * STAGE_FLOPS[dom][1] / (s_ms / 1e3) / 1e12
+        else:
+            s_ach = cnt_serial[unit] * by / (s_ms / 1e3) / 1e9
+        roof["serial"] = {"note": "same kernel with lanes=1 (nothing else on the GPU), one extra step after the "
+                                  "timed region", "achieved": s_ach, "frac": s_ach / roof["peak"],
+                          "avg_launch_ms": s_ms / max(s_launch, 1),
+                          "stage_ms": {k: round(v[0], 2) for k, v in serial.items() if v[1]}}
         roof.update({"kernel": dom, "launches": d_launch, "avg_launch_ms": d_ms / max(d_launch, 1),
                      "share_of_step": round(d_ms / total_ms, 4), "stage_share": share,
                      "peak_source": peaks["source"] + (" (sustained bf16 cuBLAS)" if roof["bound"] == "tensor" else " (copy)")})

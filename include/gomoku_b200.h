@@ -259,6 +259,9 @@ enum {
     GZ_N_STAGES = 12
 };
 int gz_set_profiling(gz_handle h, int32_t on);
+/* Number of game groups gz_search advances on separate streams from now on (gz_config.lanes; 0 = automatic,
+ * 1 = every kernel on the caller's stream: the setting stage times are meaningful under). */
+int gz_set_lanes(gz_handle h, int32_t lanes);
 int gz_get_stage_times(gz_handle h, double *h_ms /*[GZ_N_STAGES]*/, int64_t *h_launches /*[GZ_N_STAGES]*/);
 
 /* ---- counters ---------------------------------------------------------------------------------- */
