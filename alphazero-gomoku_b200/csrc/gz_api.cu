@@ -345,6 +345,12 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         }
         w.hconv_w = d + o[18]; w.hconv_b = d + o[19];
         w.hfc_wt = d + o[20]; w.hfc_b = d + o[21];
+        for (int i = 0; i < 4; ++i) {   // k_gn_block takes its biases as a kernel parameter
+            memcpy(e->bw.gn_host_bias[i], &pk.host[o[3 + 4 * i]], 64 * sizeof(float));
+            memcpy(e->bw.gn_host_bias[i] + 64, &pk.host[o[5 + 4 * i]], 64 * sizeof(float));
+        }
+        memcpy(e->bw.gn_host_head, &pk.host[o[18]], 128 * sizeof(float));
+        memcpy(e->bw.gn_host_head + 128, &pk.host[o[19]], 2 * sizeof(float));
         std::vector<uint16_t> bf;
         size_t o3[4], o1[4];
         const float *q = gnf + 1728 + 64;

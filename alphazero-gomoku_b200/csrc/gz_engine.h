@@ -51,6 +51,8 @@ struct DqnWeights {
 // bf16 tensor-core path: conv weights packed per K-step as [8 channel groups][cout][8 channels]
 // (K-major SWIZZLE_NONE core matrices), BN folded; biases and the first layer reuse the fp32 packs.
 struct Bf16Weights {
+    float gn_host_bias[4][128];   // host copies for k_gn_block's parameter block: per block b3[64], b1[64]
+    float gn_host_head[130];      // GraphNet head 1x1: w[64][2] (device layout of hconv_w), b[2]
     uint8_t *pv_tower_w[4];
     uint8_t *gn_l3_w[4];
     uint8_t *gn_l1_w[4];

@@ -67,7 +67,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16 + 2);
     float *s_hw = reinterpret_cast<float *>(bars + 32);     // HEADS: [COUT][2] policy, [COUT] value, 3 biases
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
     if (HEADS) {
         for (int i = threadIdx.x; i < 2 * COUT; i += blockDim.x) s_hw[i] = heads.pw[i];
         for (int i = threadIdx.x; i < COUT; i += blockDim.x) s_hw[2 * COUT + i] = heads.vw[i];
@@ -176,29 +176,30 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                 ptx::mbar_wait(&acc_empty[ab], par ^ 1);
                 ptx::mbar_wait(&a_full[ab], par);
                 ptx::tc_fence_after();
-                const uint32_t slab_addr = ptx::smem_u32(slab + ab * C::SLAB_BYTES);
+                // one base descriptor per operand; everything else is a compile-time constant added to the
+                // 16-byte address field (K-step loop fully unrolled)
+                const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
                 const uint32_t acc = tmem_base + ab * 2 * COUT;
+#pragma unroll
                 for (int ks = 0; ks < C::KSTEPS; ++ks) {
                     const int tap = ks / C::CHUNKS, chunk = ks - tap * C::CHUNKS;
                     constexpr int CGS = C::KSTEP / 8;       // channel groups per K-step
                     const int rowoff = TAPS == 9 ? 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1) : 0;
-                    uint32_t w_addr;
+                    uint64_t db0;
                     if (RESIDENT) {
-                        w_addr = ptx::smem_u32(wbuf + ks * C::WSTEP_BYTES);
+                        db0 = ptx::make_desc(ptx::smem_u32(wbuf) + ks * C::WSTEP_BYTES, LBO_B, 128);
                     } else {
                         ptx::mbar_wait(&b_full[wstage], wphase);
                         ptx::tc_fence_after();
-                        w_addr = ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES);
+                        db0 = ptx::make_desc(ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES), LBO_B, 128);
                     }
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
 #pragma unroll
-                        for (int k = 0; k < C::KK; ++k) {
-                            uint32_t a_addr = slab_addr + ((chunk * CGS + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h) * 16;
-                            uint32_t b_addr = w_addr + 2 * k * LBO_B;
-                            ptx::umma_bf16_elect(acc + h * COUT, ptx::make_desc(a_addr, LBO_A, 128),
-                                           ptx::make_desc(b_addr, LBO_B, 128), idesc, (ks | k) != 0);
-                        }
+                        for (int k = 0; k < C::KK; ++k)
+                            ptx::umma_bf16_elect(acc + h * COUT,
+                                                 da0 + (uint64_t)((chunk * CGS + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h),
+                                                 db0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, (ks | k) != 0);
                     }
                     if (!RESIDENT) {
                         ptx::umma_commit_elect(&b_empty[wstage]);
@@ -331,6 +332,15 @@ struct GnBlockCfg {
     static constexpr int SMEM = 2 * SLAB_BYTES + 2 * MID_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
 };
 
+// Biases (and the head's 1x1 weights) travel as a kernel parameter: after unrolling every index is a
+// compile-time constant, so the epilogue's FADD/FFMA read them straight from the constant bank.  As
+// shared-memory loads they were 17 % of the SM's shared-memory wavefronts, the resource this kernel is
+// bound by (tensor operand fetches are the other 76 %; profiles/r02_gn_block_ncu.md).
+struct GnBlockConsts {
+    float b3[64], b1[64];
+    float head_w[128], head_b[2];   // FINAL only: [64][2], [2]
+};
+
 // FINAL (the last block): the head's 1x1 convolution 64 -> 2 (bg_planner.py:43,54; no activation) is
 // applied to the fp32 epilogue values and only its 450 outputs per board are written (`head_out`
 // f32 [G][450], channel-major like the flatten at bg_planner.py:55); the 64-channel planes of the
@@ -338,8 +348,7 @@ struct GnBlockCfg {
 template <bool FINAL>
 __global__ void __launch_bounds__(320, 1)
 k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
-           const float *__restrict__ bias3, const float *__restrict__ bias1, uint8_t *__restrict__ out_planes,
-           const float *__restrict__ head_w /*[64][2]*/, const float *__restrict__ head_b /*[2]*/,
+           const __grid_constant__ GnBlockConsts kc, uint8_t *__restrict__ out_planes,
            float *__restrict__ head_out, int G) {
     using C = GnBlockCfg;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -354,12 +363,9 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     uint64_t *mid_full = bars + 8, *mid_empty = bars + 10, *d2_full = bars + 12, *d2_empty = bars + 14;
     uint64_t *w_full = bars + 16;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 17);
-    float *c_gn_head = reinterpret_cast<float *>(bars + 32);   // [64][2] head weights, then 2 biases
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
     if (FINAL) {
-        if (threadIdx.x >= 128 && threadIdx.x < 256) c_gn_head[threadIdx.x - 128] = head_w[threadIdx.x - 128];
-        if (threadIdx.x >= 256 && threadIdx.x < 258) c_gn_head[threadIdx.x - 128] = head_b[threadIdx.x - 256];
     }
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
@@ -371,8 +377,6 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
         ptx::mbar_init(w_full, 1);
         ptx::fence_mbar_init();
     }
-    if (threadIdx.x < 64) sb3[threadIdx.x] = bias3[threadIdx.x];
-    else if (threadIdx.x < 128) sb1[threadIdx.x - 64] = bias1[threadIdx.x - 64];
     if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
     ptx::tc_fence_before();
     __syncthreads();
@@ -408,9 +412,13 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     ptx::mbar_wait(&d1_empty[ab], par ^ 1);
                     ptx::mbar_wait(&a_full[ab], par);
                     ptx::tc_fence_after();
-                    const uint32_t slab_addr = ptx::smem_u32(slab + ab * C::SLAB_BYTES);
+                    // Descriptors = one base per operand + compile-time constants in the 16-byte address field:
+                    // at N = 64 a UMMA lasts 48 cycles and anything more per instruction shows (the loop is fully
+                    // unrolled: 72 instructions, two 64-bit adds each).
+                    const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
+                    const uint64_t db0 = ptx::make_desc(w3_addr, LBO_B, 128);
                     const uint32_t acc = tmem_base + ab * 128;
-#pragma unroll 1
+#pragma unroll
                     for (int tap = 0; tap < 9; ++tap) {
                         const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
 #pragma unroll
@@ -418,9 +426,9 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 ptx::umma_bf16_elect(acc + h * 64,
-                                               ptx::make_desc(slab_addr + (2 * k * C::SLAB_ROWS + rowoff + 128 * h) * 16, LBO_A, 128),
-                                               ptx::make_desc(w3_addr + tap * 8192 + 2 * k * LBO_B, LBO_B, 128),
-                                               idesc, (tap | k) != 0);
+                                                     da0 + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff + 128 * h),
+                                                     db0 + (uint64_t)((tap * 8192 + 2 * k * (int)LBO_B) >> 4),
+                                                     idesc, (tap | k) != 0);
                     }
                     ptx::umma_commit_elect(&a_empty[ab]);
                     ptx::umma_commit_elect(&d1_full[ab]);
@@ -431,15 +439,15 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     ptx::mbar_wait(&mid_full[jb], par);
                     ptx::mbar_wait(&d2_empty[jb], par ^ 1);
                     ptx::tc_fence_after();
-                    const uint32_t mid_addr = ptx::smem_u32(mid + jb * C::MID_BYTES);
+                    const uint64_t dm0 = ptx::make_desc(ptx::smem_u32(mid + jb * C::MID_BYTES), LBO_M, 128);
+                    const uint64_t dw0 = ptx::make_desc(w1_addr, LBO_B, 128);
                     const uint32_t acc = tmem_base + 256 + jb * 128;
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            ptx::umma_bf16_elect(acc + h * 64,
-                                           ptx::make_desc(mid_addr + (2 * k * 256 + 128 * h) * 16, LBO_M, 128),
-                                           ptx::make_desc(w1_addr + 2 * k * LBO_B, LBO_B, 128), idesc, k != 0);
+                            ptx::umma_bf16_elect(acc + h * 64, dm0 + (uint64_t)(2 * k * 256 + 128 * h),
+                                                 dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
                     ptx::umma_commit_elect(&mid_empty[jb]);
                     ptx::umma_commit_elect(&d2_full[jb]);
                 }
@@ -466,8 +474,8 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     uint32_t pk[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
-                        pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + sb3[c0 + 2 * i], 0.f),
-                                               fmaxf(v[2 * i + 1] + sb3[c0 + 2 * i + 1], 0.f));
+                        pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + kc.b3[c0 + 2 * i], 0.f),
+                                               fmaxf(v[2 * i + 1] + kc.b3[c0 + 2 * i + 1], 0.f));
                     *reinterpret_cast<uint4 *>(dst + (c0 / 8) * 4096) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4 *>(dst + (c0 / 8 + 1) * 4096) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
@@ -482,16 +490,16 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                 ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
                 ptx::tc_fence_after();
                 if (FINAL) {
-                    float p0 = c_gn_head[128], p1 = c_gn_head[129];
+                    float p0 = kc.head_b[0], p1 = kc.head_b[1];
 #pragma unroll
                     for (int c0 = 0; c0 < 64; c0 += 16) {
                         float v[16];
                         ptx::tmem_ld16(tlane + 256 + jb * 128 + c0, v);
 #pragma unroll
                         for (int i = 0; i < 16; ++i) {
-                            const float x = fmaxf(v[i] + sb1[c0 + i], 0.f);
-                            p0 = fmaf(c_gn_head[2 * (c0 + i)], x, p0);
-                            p1 = fmaf(c_gn_head[2 * (c0 + i) + 1], x, p1);
+                            const float x = fmaxf(v[i] + kc.b1[c0 + i], 0.f);
+                            p0 = fmaf(kc.head_w[2 * (c0 + i)], x, p0);
+                            p1 = fmaf(kc.head_w[2 * (c0 + i) + 1], x, p1);
                         }
                     }
                     if (valid) {
@@ -508,8 +516,8 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                         uint32_t pk[8];
     #pragma unroll
                         for (int i = 0; i < 8; ++i)
-                            pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + sb1[c0 + 2 * i], 0.f),
-                                                           fmaxf(v[2 * i + 1] + sb1[c0 + 2 * i + 1], 0.f)) : 0u;
+                            pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + kc.b1[c0 + 2 * i], 0.f),
+                                                           fmaxf(v[2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
                         *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                         *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                     }
@@ -525,17 +533,20 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
 }
 
-static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, const uint8_t *w1, const float *b3,
-                            const float *b1, uint8_t *out, float *head_out, int G, cudaStream_t s) {
+static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, const uint8_t *w1, int block,
+                            uint8_t *out, float *head_out, int G, cudaStream_t s) {
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(k_gn_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
         cudaFuncSetAttribute(k_gn_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
         configured = true;
     }
+    GnBlockConsts kc;
+    memcpy(kc.b3, e.bw.gn_host_bias[block], sizeof(float) * 128);   // b3 then b1
+    memcpy(kc.head_w, e.bw.gn_host_head, sizeof(float) * 130);       // head_w then head_b
     int grid = G < e.sm_count ? G : e.sm_count;
-    if (head_out) k_gn_block<true><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, b3, b1, out, e.gn.hconv_w, e.gn.hconv_b, head_out, G);
-    else k_gn_block<false><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, b3, b1, out, nullptr, nullptr, nullptr, G);
+    if (head_out) k_gn_block<true><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
+    else k_gn_block<false><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
 }
 
 // ---- host side -------------------------------------------------------------------------------------
@@ -580,7 +591,7 @@ void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *ac
     launch_conv<16, 64, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.gn_embed_w,
                                               e.gn.embed.b, nullptr, p0, active, G, s);
     for (int i = 0; i < 4; ++i) {   // p0 -> p1 -> p0 -> p1 -> p0
-        launch_gn_block(e, (i & 1) ? p1 : p0, w.gn_l3_w[i], w.gn_l1_w[i], e.gn.l3[i].b, e.gn.l1[i].b,
+        launch_gn_block(e, (i & 1) ? p1 : p0, w.gn_l3_w[i], w.gn_l1_w[i], i,
                         (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s);
     }
     prof_end(e, s);
