@@ -89,7 +89,11 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
         for (int i = 0; i < 3; ++i) CK(dalloc(&e->act[i], G * 128 * kCells));
     }
     CK(dalloc(&e->gn_logits, G * kCells)); CK(dalloc(&e->gn_policy, G * kPolicyPitch));
-    CK(dalloc(&e->pv_pc, G * 450)); CK(dalloc(&e->pv_vc, G * kCells)); CK(dalloc(&e->gn_pc, G * 450));
+    {
+        const size_t tiles = (G + 127) / 128;   // zero filled once: K padding and rows past G are never written
+        CK(dalloc(&e->pv_pc, tiles * kHeadTileBytesP)); CK(dalloc(&e->pv_vc, tiles * kHeadTileBytesV));
+        CK(dalloc(&e->gn_pc, tiles * kHeadTileBytesP));
+    }
     CK(dalloc(&e->dqn_q, G * kCells));
     CK(dalloc(&e->pv_logits, G * kCells)); CK(dalloc(&e->pv_probs, G * kCells));
     CK(dalloc(&e->pv_value, G));
@@ -639,7 +643,8 @@ static Engine *lane_view(Engine *e, int l, size_t g0) {
         v->act[i] = e->act[i] ? e->act[i] + g0 * 128 * kCells : nullptr;
     }
     v->gn_logits = e->gn_logits + g0 * kCells; v->gn_policy = e->gn_policy + g0 * kPolicyPitch;
-    v->pv_pc = e->pv_pc + g0 * 450; v->pv_vc = e->pv_vc + g0 * kCells; v->gn_pc = e->gn_pc + g0 * 450;
+    v->pv_pc = e->pv_pc + (g0 >> 7) * kHeadTileBytesP; v->pv_vc = e->pv_vc + (g0 >> 7) * kHeadTileBytesV;   // g0 % 128 == 0
+    v->gn_pc = e->gn_pc + (g0 >> 7) * kHeadTileBytesP;
     v->dqn_q = e->dqn_q + g0 * kCells;
     v->pv_logits = e->pv_logits + g0 * kCells; v->pv_probs = e->pv_probs + g0 * kCells;
     v->pv_value = e->pv_value + g0;
@@ -665,12 +670,13 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     if (c.eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_search: gz_set_pv_weights was not called");
     if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_search: planner weights not set");
     int nl = e->cfg.lanes > 0 ? e->cfg.lanes : (G >= 4096 ? 4 : G >= 1024 ? 2 : 1);
-    if (nl > G) nl = G;
+    if (nl > G / 128) nl = G / 128 > 1 ? G / 128 : 1;   // every lane owns at least one whole tile of 128 boards
     Engine *v[kMaxLanes];
     cudaStream_t ls[kMaxLanes];
     int g0[kMaxLanes + 1];
     SearchCfg lc[kMaxLanes];
-    for (int l = 0; l <= nl; ++l) g0[l] = (int)((long long)G * l / nl);
+    // lane boundaries on multiples of 128 boards: the head GEMMs work on tiles of 128 rows
+    for (int l = 0; l <= nl; ++l) g0[l] = l == nl ? G : (int)((long long)G * l / nl) & ~127;
     if (nl > 1) CK(cudaEventRecord(e->lane_go, s));
     for (int l = 0; l < nl; ++l) {
         v[l] = lane_view(e, l, (size_t)g0[l]);

@@ -20,6 +20,21 @@ constexpr int kGuardBytes = 256;
 // row pitch (floats) of the engine's internal softmax / prior rows: 225 cells padded for 16-byte stores
 constexpr int kPolicyPitch = 256;
 
+// A operand of the head GEMMs (gz_nn_fc.cu): boards in tiles of 128 rows, K in chunks of 64, every chunk a
+// bf16 "hi" block followed by a "lo" block (x = hi + lo to ~16 mantissa bits), each block 8 K-groups x 128
+// rows x 8 values -- the K-major SWIZZLE_NONE core-matrix order tcgen05.mma reads, so a chunk is one 32 KB
+// bulk copy.  The convolution epilogues that produce the values write them straight into this form.
+constexpr int kHeadBlockBytes = 8 * 128 * 16;                 // one hi or lo block
+constexpr int kHeadChunksP = 8, kHeadChunksV = 4;             // ceil(450 / 64), ceil(225 / 64)
+constexpr size_t kHeadTileBytesP = (size_t)kHeadChunksP * 2 * kHeadBlockBytes;
+constexpr size_t kHeadTileBytesV = (size_t)kHeadChunksV * 2 * kHeadBlockBytes;
+#if defined(__CUDACC__)
+__host__ __device__ __forceinline__ size_t head_operand_offset(int board, int k, int chunks) {   // of the hi value
+    return ((size_t)(board >> 7) * chunks + (k >> 6)) * 2 * kHeadBlockBytes + ((k >> 3) & 7) * 2048 +
+           (board & 127) * 16 + (k & 7) * 2;
+}
+#endif
+
 // fp32 network parameters on the device, BN folded, laid out for the FFMA kernels:
 // conv weights as [cin][tap][cout] (cout contiguous), linear weights transposed to [in][out].
 struct ConvW {
@@ -148,7 +163,9 @@ struct Engine {
     // network activations (fp32 path): three ping-pong buffers [G][128][225]
     float *act[3];
     float *gn_logits, *gn_policy, *dqn_q;   // [G][225], [G][kPolicyPitch], [G][225]
-    float *pv_pc, *pv_vc, *gn_pc;           // fused head-conv outputs: [G][450], [G][225], [G][450]
+    // fused head-conv outputs, already in the form the head GEMMs read them (head_operand_offset below):
+    // policy 450 inputs -> 8 K-chunks, value 225 -> 4, per tile of 128 boards
+    uint8_t *pv_pc, *pv_vc, *gn_pc;
     float *pv_logits, *pv_probs, *pv_value; // [G][225], [G][225], [G]
     gz_board *tmp_boards; // [G]
     uint8_t *tmp_u8;      // [G*232] host-call staging: cells, to_move, ai_player, move_count

@@ -43,13 +43,23 @@ struct ConvCfg {
 // zero); the producer warp writes the one-hot slab from the bitboards instead of copying planes.
 // HEADS (the last tower convolution of AlphaZeroGomokuNet): the 1x1 head convolutions 128 -> 2 (policy)
 // and 128 -> 1 (value), neither with BN nor activation (neural_network.py:149,154), are applied to the
-// fp32 epilogue values; only their outputs are written (heads.pc f32 [G][450] channel-major like the
-// flatten at :150, heads.vc f32 [G][225]) and the 128-channel planes of the last layer are not stored.
+// fp32 epilogue values; only their outputs are written (heads.pc: 450 values per board, K index channel-major
+// like the flatten at :150, heads.vc: 225 values; both as bf16 hi/lo operand tiles of the head GEMMs) and the
+// 128-channel planes of the last layer are not stored.
 struct HeadConv {
     const float *pw, *pb;   // [COUT][2], [2]
     const float *vw, *vb;   // [COUT], [1]
-    float *pc, *vc;
+    uint8_t *pc, *vc;       // bf16 hi/lo operand tiles of the head GEMMs (head_operand_offset, gz_engine.h)
 };
+
+// x as bf16 hi + lo parts, stored at the value's place in a head operand tile
+__device__ __forceinline__ void store_head_operand(uint8_t *tile_base, int board, int k, int chunks, float x) {
+    const uint32_t hl = ptx::pack_bf16(x, 0.f) & 0xFFFFu;
+    const float r = x - __uint_as_float(hl << 16);
+    uint8_t *dst = tile_base + head_operand_offset(board, k, chunks);
+    *reinterpret_cast<uint16_t *>(dst) = (uint16_t)hl;
+    *reinterpret_cast<uint16_t *>(dst + kHeadBlockBytes) = (uint16_t)(ptx::pack_bf16(r, 0.f) & 0xFFFFu);
+}
 
 template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false, bool HEADS = false>
 __global__ void __launch_bounds__(192, 1)
@@ -268,9 +278,9 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             }
             if (HEADS && valid) {
                 const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
-                heads.pc[(size_t)b * 450 + cell] = hp0;
-                heads.pc[(size_t)b * 450 + kCells + cell] = hp1;
-                heads.vc[(size_t)b * kCells + cell] = hv0;
+                store_head_operand(heads.pc, b, cell, kHeadChunksP, hp0);
+                store_head_operand(heads.pc, b, kCells + cell, kHeadChunksP, hp1);
+                store_head_operand(heads.vc, b, cell, kHeadChunksV, hv0);
             }
         };
         auto next_board = [&](int b) {
@@ -342,14 +352,14 @@ struct GnBlockConsts {
 };
 
 // FINAL (the last block): the head's 1x1 convolution 64 -> 2 (bg_planner.py:43,54; no activation) is
-// applied to the fp32 epilogue values and only its 450 outputs per board are written (`head_out`
-// f32 [G][450], channel-major like the flatten at bg_planner.py:55); the 64-channel planes of the
+// applied to the fp32 epilogue values and only its 450 outputs per board are written (`head_out`:
+// bf16 hi/lo operand tiles of the head GEMM, K index channel-major like the flatten at bg_planner.py:55); the 64-channel planes of the
 // last layer are never stored.
 template <bool FINAL>
 __global__ void __launch_bounds__(320, 1)
 k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
            const __grid_constant__ GnBlockConsts kc, uint8_t *__restrict__ out_planes,
-           float *__restrict__ head_out, int G) {
+           uint8_t *__restrict__ head_out, int G) {
     using C = GnBlockCfg;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *slab = smem;
@@ -504,8 +514,8 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     }
                     if (valid) {
                         const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
-                        head_out[(size_t)b * 450 + cell] = p0;
-                        head_out[(size_t)b * 450 + kCells + cell] = p1;
+                        store_head_operand(head_out, b, cell, kHeadChunksP, p0);
+                        store_head_operand(head_out, b, kCells + cell, kHeadChunksP, p1);
                     }
                 } else {
                 uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
@@ -534,7 +544,7 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
 }
 
 static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, const uint8_t *w1, int block,
-                            uint8_t *out, float *head_out, int G, cudaStream_t s) {
+                            uint8_t *out, uint8_t *head_out, int G, cudaStream_t s) {
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(k_gn_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);

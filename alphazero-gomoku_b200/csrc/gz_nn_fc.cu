@@ -213,14 +213,17 @@ void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStr
 // The A operand (fp32 head-conv outputs) is split into bf16 hi + lo parts, both multiplied by the
 // same bf16 weights, so the activations keep fp32-like accuracy.  Thread = board row in the epilogue.
 namespace {
-constexpr int kHdChunksP = 8, kHdChunksV = 4;
+constexpr int kHdChunksP = kHeadChunksP, kHdChunksV = kHeadChunksV;
 constexpr int kHdWBytesP = 8 * 256 * 16, kHdWBytesV = 8 * 64 * 16;
-constexpr int kSmemHead = 2 * 2 * kChunkBytesA + kWStages * kHdWBytesP + (256 + 64 + 64 + 4) * 4 + 256;
+constexpr int kStageRow = 36;                       // floats per staged row: 32 values + 4 pad (16-byte aligned rows)
+constexpr int kStageBytes = 32 * kStageRow * 4;     // per epilogue warp: 32 rows x 32 columns
+constexpr int kSmemHead = 2 * 2 * kChunkBytesA + kWStages * kHdWBytesP + 4 * kStageBytes + (256 + 64 + 64 + 4) * 4 + 256;
+static_assert(kChunkBytesA == kHeadBlockBytes, "head operand tiles are copied chunk by chunk into the A buffers");
 }  // namespace
 
 struct HeadArgs {
-    const float *pc;          // [G][450] policy head conv outputs
-    const float *vc;          // [G][225] value head conv outputs (PV)
+    const uint8_t *pc;        // policy head conv outputs, bf16 hi/lo operand tiles (gz_engine.h)
+    const uint8_t *vc;        // value head conv outputs (PV), likewise
     const gz_board *boards;   // legal mask for the prior (PV)
     const uint8_t *active;    // optional per-board mask
     const uint8_t *w_pol;     // 8 chunks [8 kg][256][8] bf16
@@ -237,17 +240,34 @@ struct HeadArgs {
     int G;
 };
 
-__device__ __forceinline__ void split_store_hi_lo(uint8_t *hi, uint8_t *lo, const float *x) {
-    uint32_t h[4], l[4];
+// Epilogue stores: a thread owns one board row, so storing its values directly makes every warp store touch
+// 32 different rows (16 bytes each).  Instead the warp parks a 32 x 32 block in its staging tile and writes it
+// back row by row: 128 contiguous bytes per row, 4 rows per instruction (vector form, 16-byte aligned rows of
+// pitch kPolicyPitch) or one row per instruction (scalar form, the [G][225] API outputs).
+__device__ __forceinline__ void stage_block(float *stage, int lane, const float *vals) {
+    __syncwarp();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        h[j] = ptx::pack_bf16(x[2 * j], x[2 * j + 1]);                       // one cvt.rn.bf16x2.f32
-        const float r0 = x[2 * j] - __uint_as_float(h[j] << 16);
-        const float r1 = x[2 * j + 1] - __uint_as_float(h[j] & 0xFFFF0000u);
-        l[j] = ptx::pack_bf16(r0, r1);
+    for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4 *>(stage + lane * kStageRow + j) = make_float4(vals[j], vals[j + 1], vals[j + 2], vals[j + 3]);
+    __syncwarp();
+}
+__device__ __forceinline__ void store_rows_vec(float *stage, int lane, const float *vals, float *row_ptr, int c0) {
+    stage_block(stage, lane, vals);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = 4 * i + (lane >> 3), c4 = (lane & 7) * 4;
+        float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
+        const float4 x = *reinterpret_cast<const float4 *>(stage + r * kStageRow + c4);
+        if (dst) *reinterpret_cast<float4 *>(dst + c0 + c4) = x;
     }
-    *reinterpret_cast<uint4 *>(hi) = make_uint4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<uint4 *>(lo) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+__device__ __forceinline__ void store_rows_scalar(float *stage, int lane, const float *vals, float *row_ptr, int c0, int ncols) {
+    stage_block(stage, lane, vals);
+#pragma unroll 4
+    for (int r = 0; r < 32; ++r) {
+        float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
+        if (dst && c0 + lane < ncols) dst[c0 + lane] = stage[r * kStageRow + lane];
+    }
 }
 
 template <bool PV>
@@ -255,7 +275,8 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *abuf = smem;                                   // [2 buffers][hi, lo][kChunkBytesA]
     uint8_t *wbuf = abuf + 4 * kChunkBytesA;                // [kWStages][kHdWBytesP]
-    float *s_bp = reinterpret_cast<float *>(wbuf + kWStages * kHdWBytesP);
+    float *stage_all = reinterpret_cast<float *>(wbuf + kWStages * kHdWBytesP);   // [4 warps][32][kStageRow]
+    float *s_bp = stage_all + 4 * 32 * kStageRow;
     float *s_b1 = s_bp + 256, *s_w2 = s_b1 + 64, *s_b2 = s_w2 + 64;
     uint64_t *bars = reinterpret_cast<uint64_t *>(s_b2 + 4);
     uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *b_empty = bars + 7, *d_full = bars + 10;
@@ -265,7 +286,7 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x;
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&a_full[i], 128); ptx::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < kWStages; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
         ptx::mbar_init(&d_full[0], 1); ptx::mbar_init(&d_full[1], 1);
         ptx::fence_mbar_init();
@@ -292,6 +313,14 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
                 ptx::mbar_expect_tx(&b_full[st], bytes);
                 ptx::bulk_g2s(wbuf + st * kHdWBytesP, src, bytes / 2, &b_full[st]);
                 ptx::bulk_g2s(wbuf + st * kHdWBytesP + bytes / 2, src + bytes / 2, bytes / 2, &b_full[st]);
+                // activations of this chunk: hi block then lo block, written in place by the conv epilogues
+                const int ab = i & 1;
+                const uint8_t *asrc = pol ? a.pc + (size_t)tile * kHeadTileBytesP + (size_t)i * 2 * kChunkBytesA
+                                          : a.vc + (size_t)tile * kHeadTileBytesV + (size_t)(i - kHdChunksP) * 2 * kChunkBytesA;
+                ptx::mbar_wait(&a_empty[ab], ((i >> 1) & 1) ^ 1);
+                ptx::mbar_expect_tx(&a_full[ab], 2 * kChunkBytesA);
+                ptx::bulk_g2s(abuf + 2 * ab * kChunkBytesA, asrc, kChunkBytesA, &a_full[ab]);
+                ptx::bulk_g2s(abuf + (2 * ab + 1) * kChunkBytesA, asrc + kChunkBytesA, kChunkBytesA, &a_full[ab]);
             }
         }
     } else if (warp == 1) {
@@ -329,43 +358,21 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
         const int b = tile * 128 + m;
         const bool live = b < a.G && (!a.active || a.active[b]);
         const int bb = b < a.G ? b : a.G - 1;              // rows past the end read a valid board, write nothing
-        // ---- operand chunks: 64 inputs of every board row, fp32 -> bf16 hi + lo.  Eight lanes share a row
-        // (one k-group of 8 inputs each) so that a warp instruction touches 4 rows x 256 contiguous bytes.
-        const int wq = warp - 2;                           // rows 32*wq .. 32*wq + 31 are generated by this warp
-        for (int i = 0; i < kChunks; ++i) {
-            const int ab = i & 1;
-            const bool pol = i < kHdChunksP;
-            const int kreal = pol ? 450 : kCells;
-            const int k0 = 64 * (pol ? i : i - kHdChunksP) + 8 * (lane & 7);
-            ptx::mbar_wait(&a_empty[ab], ((i >> 1) & 1) ^ 1);
-#pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                const int row = 32 * wq + 4 * t + (lane >> 3);
-                int gb = tile * 128 + row;
-                if (gb >= a.G) gb = a.G - 1;
-                const float *src = (pol ? a.pc + (size_t)gb * 450 : a.vc + (size_t)gb * kCells) + k0;
-                float x[8];
-#pragma unroll
-                for (int j = 0; j < 8; j += 2) {
-                    if (pol) {                               // 450-float rows are 8-byte aligned
-                        float2 v2 = k0 + j < kreal ? __ldg(reinterpret_cast<const float2 *>(src + j)) : make_float2(0.f, 0.f);
-                        x[j] = v2.x; x[j + 1] = v2.y;
-                    } else {                                 // 225-float rows are only 4-byte aligned
-                        x[j] = k0 + j < kreal ? __ldg(src + j) : 0.f;
-                        x[j + 1] = k0 + j + 1 < kreal ? __ldg(src + j + 1) : 0.f;
-                    }
-                }
-                uint8_t *hi = abuf + (2 * ab) * kChunkBytesA + (lane & 7) * 128 * 16 + row * 16;
-                split_store_hi_lo(hi, hi + kChunkBytesA, x);
-            }
-            ptx::fence_proxy_async();
-            ptx::mbar_arrive(&a_full[ab]);
-        }
+        const int wq = warp - 2;
+#ifdef GZ_HEAD_TIMING
+        long long tt[8]; tt[0] = clock64();
+#endif
+#ifdef GZ_HEAD_TIMING
+        tt[1] = clock64();
+#endif
         const uint32_t trow = tmem_base + ((uint32_t)(32 * qd) << 16);
         // ---- policy: softmax over the 225 logits of this row (two passes over tensor memory: an online
         // max / sum, then the normalised values; exp through ex2.approx like __expf)
         ptx::mbar_wait(&d_full[0], 0);
         ptx::tc_fence_after();
+#ifdef GZ_HEAD_TIMING
+        tt[2] = clock64();
+#endif
         constexpr float kLog2e = 1.4426950408889634f;
         float mx = -INFINITY, sum = 0.f;
 #pragma unroll 1
@@ -385,6 +392,9 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
             sum = sum * exp2f((mx - nm) * kLog2e) + cs;
             mx = nm;
         }
+#ifdef GZ_HEAD_TIMING
+        tt[3] = clock64();
+#endif
         const float inv = 1.f / sum;
         uint32_t legal[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (PV && a.prior) {
@@ -392,44 +402,47 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
             bb_to_raster(e, legal);
         }
         float legal_sum = 0.f;
-        float *pol_row = a.policy ? a.policy + (size_t)bb * kPolicyPitch : nullptr;
+        float *stage = stage_all + wq * 32 * kStageRow;
+        float *pol_row = a.policy && live ? a.policy + (size_t)b * kPolicyPitch : nullptr;
+        float *lg_row = a.logits && live ? a.logits + (size_t)b * kCells : nullptr;
+        float *pb_row = a.probs && live ? a.probs + (size_t)b * kCells : nullptr;
 #pragma unroll 1
-        for (int c0 = 0; c0 < 240; c0 += 16) {
-            float v[16], pr[16];
+        for (int c0 = 0; c0 < 256; c0 += 32) {
+            float v[32], pr[32];
             ptx::tmem_ld16(trow + c0, v);
-            const uint32_t lbits = (legal[c0 >> 5] >> (c0 & 31)) & 0xFFFFu;
+            ptx::tmem_ld16(trow + c0 + 16, v + 16);
+            const uint32_t lbits = legal[c0 >> 5];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float lg = v[j] + s_bp[c0 + j];
-                pr[j] = c0 + j < kCells ? exp2f((lg - mx) * kLog2e) * inv : 0.f;
+            for (int j = 0; j < 32; ++j) {
+                v[j] += s_bp[c0 + j];
+                pr[j] = c0 + j < kCells ? exp2f((v[j] - mx) * kLog2e) * inv : 0.f;
                 if (PV && ((lbits >> j) & 1u)) legal_sum += pr[j];
-                if (live && a.logits && c0 + j < kCells) a.logits[(size_t)b * kCells + c0 + j] = lg;
-                if (live && a.probs && c0 + j < kCells) a.probs[(size_t)b * kCells + c0 + j] = pr[j];
             }
-            if (live && pol_row) {
-#pragma unroll
-                for (int j = 0; j < 16; j += 4)
-                    *reinterpret_cast<float4 *>(pol_row + c0 + j) = make_float4(pr[j], pr[j + 1], pr[j + 2], pr[j + 3]);
-            }
+            if (a.logits) store_rows_scalar(stage, lane, v, lg_row, c0, kCells);
+            if (a.probs) store_rows_scalar(stage, lane, pr, pb_row, c0, kCells);
+            if (a.policy) store_rows_vec(stage, lane, pr, pol_row, c0);
         }
+#ifdef GZ_HEAD_TIMING
+        tt[4] = clock64();
+#endif
         if (PV && a.prior) {   // warp-uniform: tcgen05.ld is .sync.aligned, only the stores are per-row
-            float *dst = a.prior + ((size_t)bb * a.prior_cap + (live ? a.prior_slot[bb] : 0)) * kPolicyPitch;
+            float *dst = live ? a.prior + ((size_t)b * a.prior_cap + a.prior_slot[b]) * kPolicyPitch : nullptr;
             const float scale = legal_sum > 0.f ? inv / legal_sum : inv;   // prior = p / sum of legal p (ai_agent.py:573-582)
 #pragma unroll 1
-            for (int c0 = 0; c0 < 240; c0 += 16) {
-                float v[16], o[16];
+            for (int c0 = 0; c0 < 256; c0 += 32) {
+                float v[32];
                 ptx::tmem_ld16(trow + c0, v);
-                const uint32_t lbits = (legal[c0 >> 5] >> (c0 & 31)) & 0xFFFFu;
+                ptx::tmem_ld16(trow + c0 + 16, v + 16);
+                const uint32_t lbits = legal[c0 >> 5];
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    o[j] = ((lbits >> j) & 1u) ? exp2f((v[j] + s_bp[c0 + j] - mx) * kLog2e) * scale : 0.f;
-                if (live) {
-#pragma unroll
-                    for (int j = 0; j < 16; j += 4)
-                        *reinterpret_cast<float4 *>(dst + c0 + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
-                }
+                for (int j = 0; j < 32; ++j)
+                    v[j] = ((lbits >> j) & 1u) ? exp2f((v[j] + s_bp[c0 + j] - mx) * kLog2e) * scale : 0.f;
+                store_rows_vec(stage, lane, v, dst, c0);
             }
         }
+#ifdef GZ_HEAD_TIMING
+        tt[5] = clock64();
+#endif
         if (PV) {
             ptx::mbar_wait(&d_full[1], 0);
             ptx::tc_fence_after();
@@ -447,6 +460,12 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
                 if (a.vhead && a.prior_slot) a.vhead[(size_t)b * a.prior_cap + a.prior_slot[b]] = vv;
             }
         }
+#ifdef GZ_HEAD_TIMING
+        tt[6] = clock64();
+        if (blockIdx.x == 0 && threadIdx.x == 64)
+            printf("head PV=%d: operands %lld, wait mma %lld, softmax pass1 %lld, pass2+stores %lld, prior %lld, value %lld cycles\n",
+                   (int)PV, tt[1] - tt[0], tt[2] - tt[1], tt[3] - tt[2], tt[4] - tt[3], tt[5] - tt[4], tt[6] - tt[5]);
+#endif
     }
     ptx::tc_fence_before();
     __syncthreads();

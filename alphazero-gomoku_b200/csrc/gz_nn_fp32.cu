@@ -364,7 +364,8 @@ void nn_planner_forward(Engine &e, const gz_board *boards, int G, float *gn_logi
     if (e.cfg.precision == 1) {
         nn_graphnet_convs_bf16(e, boards, nullptr, G, s);      // ends with the fused head conv -> e.gn_pc
         const bool internal = policy_pitch == kPolicyPitch;
-        nn_heads_bf16(e, false, boards, nullptr, G, internal ? gn_policy : nullptr, gn_logits,
+        // the search and the planner only read the softmax (pitch kPolicyPitch); logits are an API output
+        nn_heads_bf16(e, false, boards, nullptr, G, internal ? gn_policy : nullptr, internal ? nullptr : gn_logits,
                       internal ? nullptr : gn_policy, nullptr, nullptr, nullptr, s);
         nn_dqn_bf16(e, boards, G, dqn_q, s);
     } else {
