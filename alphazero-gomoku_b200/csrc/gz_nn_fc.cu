@@ -30,6 +30,41 @@ constexpr int kSmemDqn = 128 * kVecBytes + 2 * kChunkBytesA + kA2Bytes + kWStage
                          3 * kFcN * 4 + 256;
 }  // namespace
 
+namespace {
+constexpr int kStageRow = 36;                       // floats per staged row: 32 values + 4 pad (16-byte aligned rows)
+constexpr int kStageBytes = 32 * kStageRow * 4;     // per epilogue warp: 32 rows x 32 columns
+}  // namespace
+
+// Epilogue stores: a thread owns one board row, so storing its values directly makes every warp store touch
+// 32 different rows (16 bytes each).  Instead the warp parks a 32 x 32 block in its staging tile and writes it
+// back row by row: 128 contiguous bytes per row, 4 rows per instruction (vector form, 16-byte aligned rows of
+// pitch kPolicyPitch) or one row per instruction (scalar form, the [G][225] API outputs).
+__device__ __forceinline__ void stage_block(float *stage, int lane, const float *vals) {
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4 *>(stage + lane * kStageRow + j) = make_float4(vals[j], vals[j + 1], vals[j + 2], vals[j + 3]);
+    __syncwarp();
+}
+__device__ __forceinline__ void store_rows_vec(float *stage, int lane, const float *vals, float *row_ptr, int c0) {
+    stage_block(stage, lane, vals);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = 4 * i + (lane >> 3), c4 = (lane & 7) * 4;
+        float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
+        const float4 x = *reinterpret_cast<const float4 *>(stage + r * kStageRow + c4);
+        if (dst) *reinterpret_cast<float4 *>(dst + c0 + c4) = x;
+    }
+}
+__device__ __forceinline__ void store_rows_scalar(float *stage, int lane, const float *vals, float *row_ptr, int c0, int ncols) {
+    stage_block(stage, lane, vals);
+#pragma unroll 4
+    for (int r = 0; r < 32; ++r) {
+        float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
+        if (dst && c0 + lane < ncols) dst[c0 + lane] = stage[r * kStageRow + lane];
+    }
+}
+
 __global__ void __launch_bounds__(192, 1)
 k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict__ w_packed,
            const float *__restrict__ bias /*[3][256]*/, float *__restrict__ q) {
@@ -159,6 +194,20 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
             ptx::tc_fence_after();
             const uint32_t tcol = trow + (layer == 1 ? kFcN : 0);
             const float *bs = sbias + layer * kFcN;
+            if (layer == 2) {   // Q values: rows written coalesced through a staging tile (the A buffers are free now)
+                float *stage = reinterpret_cast<float *>(abuf) + (warp - 2) * 32 * kStageRow;
+                float *q_row = b < G ? q + (size_t)b * kCells : nullptr;
+#pragma unroll 1
+                for (int c0 = 0; c0 < kFcN; c0 += 32) {
+                    float v[32];
+                    ptx::tmem_ld16(tcol + c0, v);
+                    ptx::tmem_ld16(tcol + c0 + 16, v + 16);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += bs[c0 + i];
+                    store_rows_scalar(stage, lane, v, q_row, c0, kCells);
+                }
+                break;
+            }
 #pragma unroll 1
             for (int c0 = 0; c0 < kFcN; c0 += 16) {
                 float v[16];
@@ -172,10 +221,6 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
                     uint8_t *dst = a2 + (c0 / 8) * 128 * 16 + m * 16;
                     *reinterpret_cast<uint4 *>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4 *>(dst + 128 * 16) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                } else if (b < G) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (c0 + i < kCells) q[(size_t)b * kCells + c0 + i] = v[i] + bs[c0 + i];
                 }
             }
             if (layer < 2) {
@@ -215,8 +260,6 @@ void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStr
 namespace {
 constexpr int kHdChunksP = kHeadChunksP, kHdChunksV = kHeadChunksV;
 constexpr int kHdWBytesP = 8 * 256 * 16, kHdWBytesV = 8 * 64 * 16;
-constexpr int kStageRow = 36;                       // floats per staged row: 32 values + 4 pad (16-byte aligned rows)
-constexpr int kStageBytes = 32 * kStageRow * 4;     // per epilogue warp: 32 rows x 32 columns
 constexpr int kSmemHead = 2 * 2 * kChunkBytesA + kWStages * kHdWBytesP + 4 * kStageBytes + (256 + 64 + 64 + 4) * 4 + 256;
 static_assert(kChunkBytesA == kHeadBlockBytes, "head operand tiles are copied chunk by chunk into the A buffers");
 }  // namespace
@@ -239,36 +282,6 @@ struct HeadArgs {
     float *vhead;
     int G;
 };
-
-// Epilogue stores: a thread owns one board row, so storing its values directly makes every warp store touch
-// 32 different rows (16 bytes each).  Instead the warp parks a 32 x 32 block in its staging tile and writes it
-// back row by row: 128 contiguous bytes per row, 4 rows per instruction (vector form, 16-byte aligned rows of
-// pitch kPolicyPitch) or one row per instruction (scalar form, the [G][225] API outputs).
-__device__ __forceinline__ void stage_block(float *stage, int lane, const float *vals) {
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < 32; j += 4)
-        *reinterpret_cast<float4 *>(stage + lane * kStageRow + j) = make_float4(vals[j], vals[j + 1], vals[j + 2], vals[j + 3]);
-    __syncwarp();
-}
-__device__ __forceinline__ void store_rows_vec(float *stage, int lane, const float *vals, float *row_ptr, int c0) {
-    stage_block(stage, lane, vals);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int r = 4 * i + (lane >> 3), c4 = (lane & 7) * 4;
-        float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
-        const float4 x = *reinterpret_cast<const float4 *>(stage + r * kStageRow + c4);
-        if (dst) *reinterpret_cast<float4 *>(dst + c0 + c4) = x;
-    }
-}
-__device__ __forceinline__ void store_rows_scalar(float *stage, int lane, const float *vals, float *row_ptr, int c0, int ncols) {
-    stage_block(stage, lane, vals);
-#pragma unroll 4
-    for (int r = 0; r < 32; ++r) {
-        float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
-        if (dst && c0 + lane < ncols) dst[c0 + lane] = stage[r * kStageRow + lane];
-    }
-}
 
 template <bool PV>
 __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
