@@ -669,7 +669,9 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     if (c.S < 1 || c.S > e->cfg.max_simulations) return fail(GZ_ERR_ARG, "gz_search: num_simulations out of range");
     if (c.eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_search: gz_set_pv_weights was not called");
     if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_search: planner weights not set");
-    int nl = e->cfg.lanes > 0 ? e->cfg.lanes : (G >= 4096 ? 4 : G >= 1024 ? 2 : 1);
+    // automatic: one lane.  Since the tensor kernels issue at full rate each of them fills the machine and
+    // two to four lanes measure within 2 % of one (profiles/r02_lanes.md); more lanes stay available on request
+    int nl = e->cfg.lanes > 0 ? e->cfg.lanes : 1;
     if (nl > G / 128) nl = G / 128 > 1 ? G / 128 : 1;   // every lane owns at least one whole tile of 128 boards
     Engine *v[kMaxLanes];
     cudaStream_t ls[kMaxLanes];

@@ -57,8 +57,9 @@ typedef struct {
     int32_t store_priors;    /* keep MCTSNode.prior_prob per node (ai_agent.py:523,564-582) */
     int32_t lanes;           /* gz_search splits its G games into this many independent groups, each
                                 advanced on its own CUDA stream so that one group's integer kernels
-                                overlap another's tensor kernels; 0 = default (4 when G >= 4096, 2 when G >= 1024).
-                                Results do not depend on it (games are independent). */
+                                may overlap another's tensor kernels; 0 = default (1: every kernel fills the
+                                GPU by itself, 2-4 lanes measure within 2 % of one).  Lane boundaries fall on
+                                multiples of 128 games.  Results do not depend on it (games are independent). */
 } gz_config;
 
 /* Mirrors AlphaZeroGomokuAI.params + ctor arguments (ai_agent.py:29-31,65-92) and
