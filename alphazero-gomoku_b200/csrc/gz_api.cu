@@ -670,7 +670,7 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     if (c.eval_nodes && !e->have_pv) return fail(GZ_ERR_STATE, "gz_search: gz_set_pv_weights was not called");
     if (c.planner_steps > 0 && !e->have_planner) return fail(GZ_ERR_STATE, "gz_search: planner weights not set");
     // automatic: one lane.  Since the tensor kernels issue at full rate each of them fills the machine and
-    // two to four lanes measure within 2 % of one (profiles/r02_lanes.md); more lanes stay available on request
+    // two to four lanes measure within 2 % of one (profiles/r01_lanes.md); more lanes stay available on request
     int nl = e->cfg.lanes > 0 ? e->cfg.lanes : 1;
     if (nl > G / 128) nl = G / 128 > 1 ? G / 128 : 1;   // every lane owns at least one whole tile of 128 boards
     Engine *v[kMaxLanes];

@@ -343,9 +343,9 @@ struct GnBlockCfg {
 };
 
 // Biases (and the head's 1x1 weights) travel as a kernel parameter: after unrolling every index is a
-// compile-time constant, so the epilogue's FADD/FFMA read them straight from the constant bank.  As
-// shared-memory loads they were 17 % of the SM's shared-memory wavefronts, the resource this kernel is
-// bound by (tensor operand fetches are the other 76 %; profiles/r02_gn_block_ncu.md).
+// compile-time constant, so the epilogue's FADD/FFMA read them straight from the constant bank / uniform
+// registers.  As shared-memory loads they were 17 % of the SM's shared-memory wavefronts, the resource this
+// kernel is bound by (tensor operand fetches are the rest; profiles/r01_gn_block_ncu_full.md).
 struct GnBlockConsts {
     float b3[64], b1[64];
     float head_w[128], head_b[2];   // FINAL only: [64][2], [2]
