@@ -179,6 +179,12 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's main kernel, from the committed
+# `ncu --set full` capture (profiles/r01_gn_block_ncu_full.md: k_gn_block, 4096 boards: 151.1 MB + 87.6 MB;
+# algorithmic 151.0 MB in + 151.0 MB out, part of the output still sits in L2 when the kernel ends)
+NCU_TRAFFIC = {"gn_convs": 238.7e6}
+
+
 def run_engine(args):
     import torch
     import engine
@@ -278,7 +284,8 @@ def run_engine(args):
             unit, f = STAGE_FLOPS[dom]
             achieved = cnt[unit] * f / (d_ms / 1e3) / 1e12
             roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"],
-                    "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"], "traffic": None}
+                    "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
+                    "traffic": NCU_TRAFFIC.get(dom)}
         else:
             unit, by = STAGE_BYTES.get(dom, ("simulations", 0))
             achieved = cnt[unit] * by / (d_ms / 1e3) / 1e9
