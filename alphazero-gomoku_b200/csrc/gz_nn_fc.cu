@@ -30,6 +30,14 @@ constexpr int kSmemDqn = 128 * kVecBytes + 2 * kChunkBytesA + kA2Bytes + kWStage
                          3 * kFcN * 4 + 256;
 }  // namespace
 
+// 2^x by one MUFU.EX2 (ex2.approx.ftz: ~2 ulp, results below 2^-126 flush to zero).  exp2f() wraps the same
+// instruction in a per-element branch for denormal results -- most of the softmax passes' time.
+__device__ __forceinline__ float fast_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 namespace {
 constexpr int kStageRow = 36;                       // floats per staged row: 32 values + 4 pad (16-byte aligned rows)
 constexpr int kStageBytes = 32 * kStageRow * 4;     // per epilogue warp: 32 rows x 32 columns
@@ -401,8 +409,8 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
             const float nm = fmaxf(mx, cm);
             float cs = 0.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) cs += exp2f((v[j] - nm) * kLog2e);
-            sum = sum * exp2f((mx - nm) * kLog2e) + cs;
+            for (int j = 0; j < 16; ++j) cs += fast_ex2((v[j] - nm) * kLog2e);
+            sum = sum * fast_ex2((mx - nm) * kLog2e) + cs;
             mx = nm;
         }
 #ifdef GZ_HEAD_TIMING
@@ -428,7 +436,7 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
                 v[j] += s_bp[c0 + j];
-                pr[j] = c0 + j < kCells ? exp2f((v[j] - mx) * kLog2e) * inv : 0.f;
+                pr[j] = c0 + j < kCells ? fast_ex2((v[j] - mx) * kLog2e) * inv : 0.f;
                 if (PV && ((lbits >> j) & 1u)) legal_sum += pr[j];
             }
             if (a.logits) store_rows_scalar(stage, lane, v, lg_row, c0, kCells);
@@ -449,7 +457,7 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
                 const uint32_t lbits = legal[c0 >> 5];
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                    v[j] = ((lbits >> j) & 1u) ? exp2f((v[j] + s_bp[c0 + j] - mx) * kLog2e) * scale : 0.f;
+                    v[j] = ((lbits >> j) & 1u) ? fast_ex2((v[j] + s_bp[c0 + j] - mx) * kLog2e) * scale : 0.f;
                 store_rows_vec(stage, lane, v, dst, c0);
             }
         }
