@@ -89,6 +89,9 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
     }
 }
 
+// Sixteen lanes per board, one candidate each: the gathers of the <= 16 candidates' policy and Q values are one
+// round trip instead of a dependent chain per candidate (a thread per board spent 18 us on 4096 boards waiting
+// for them).  Lane 0 of the group then rolls the explore dice and plays the move.
 __global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boards,
                                                       int32_t *__restrict__ steps, int G, SearchCfg c,
                                                       int sim, int step_override,
@@ -99,27 +102,39 @@ __global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boa
                                                       double *__restrict__ composed,
                                                       int32_t *__restrict__ move_out, int apply_move,
                                                       unsigned long long *__restrict__ counters) {
-    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    static_assert(kMaxTopK == 16, "one lane per candidate");
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+    const int sub = threadIdx.x & 15;
+    const bool in_range = g < G;
+    const int gi = in_range ? g : G - 1;
     int did = 0;
-    if (g < G) {
-        int n = ntop[g];
+    const int n = ntop[gi];
+    const int idx = sub < n ? topk[gi * kMaxTopK + sub] : -1;
+    double comp = -1e18;
+    if (idx >= 0) {
+        const double a = c.alpha, na = 1.0 - c.alpha;
+        comp = __dsub_rn(__dmul_rn(a, (double)policy[(size_t)gi * kPolicyPitch + idx]),
+                         __dmul_rn(na, (double)q[(size_t)gi * kCells + idx]));
+    }
+    if (composed && in_range) composed[g * kMaxTopK + sub] = idx >= 0 ? comp : 0.0;
+    // first maximum among the group's candidates: larger value, then smaller candidate index
+    double best = comp;
+    int best_j = idx >= 0 ? sub : 16, best_idx = idx;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o, 16);
+        const int oj = __shfl_xor_sync(0xffffffffu, best_j, o, 16);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_idx, o, 16);
+        if (oj < 16 && (best_j == 16 || ob > best || (ob == best && oj < best_j))) { best = ob; best_j = oj; best_idx = oi; }
+    }
+    if (in_range && sub == 0) {
         int mv = -1;
         if (n > 0) {
-            int step = step_override >= 0 ? step_override : steps[g];
-            double best_score = -1e18;
-            int best = -1;
-            double a = c.alpha, na = 1.0 - c.alpha;
-            for (int j = 0; j < n; ++j) {
-                int idx = topk[g * kMaxTopK + j];
-                double comp = __dsub_rn(__dmul_rn(a, (double)policy[(size_t)g * kPolicyPitch + idx]),
-                                        __dmul_rn(na, (double)q[(size_t)g * kCells + idx]));
-                if (composed) composed[g * kMaxTopK + j] = comp;
-                if (comp > best_score) { best_score = comp; best = idx; }   // strict: first maximum
-            }
+            const int step = step_override >= 0 ? step_override : steps[g];
             RolloutRng rng = {c.seed_lo, c.seed_hi, c.game_base + (uint32_t)g, (uint32_t)sim, c.deterministic != 0};
             // random.random() is always drawn (bg_planner.py:267)
             if (rng_random(rng, step) < c.explore) mv = topk[g * kMaxTopK + rng_choice(rng, step, n)];
-            else mv = best >= 0 ? best : topk[g * kMaxTopK];
+            else mv = best_idx >= 0 ? best_idx : topk[g * kMaxTopK];
             if (apply_move) {
                 gz_board b = boards[g];
                 board_place(b, cell_to_bit(mv));
@@ -128,7 +143,6 @@ __global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boa
                 did = 1;
             }
         }
-        if (composed) for (int j = (n > 0 ? n : 0); j < kMaxTopK; ++j) composed[g * kMaxTopK + j] = 0.0;
         if (move_out) move_out[g] = mv;
     }
     for (int o = 16; o > 0; o >>= 1) did += __shfl_xor_sync(0xffffffffu, did, o);
@@ -148,7 +162,7 @@ void launch_planner_pick(gz_board *b, const uint8_t *ai_player, int32_t *steps, 
                          double *composed, int32_t *move_out, bool apply_move,
                          unsigned long long *counters, cudaStream_t s) {
     (void)ai_player;
-    k_planner_pick<<<(G + 127) / 128, 128, 0, s>>>(b, steps, G, c, sim, planner_step, topk, ntop,
+    k_planner_pick<<<(G * 16 + 127) / 128, 128, 0, s>>>(b, steps, G, c, sim, planner_step, topk, ntop,
                                                    gn_policy, dqn_q, composed, move_out,
                                                    apply_move ? 1 : 0, counters);
 }

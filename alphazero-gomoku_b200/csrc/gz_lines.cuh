@@ -55,12 +55,12 @@ GZ_HD void line_cell(int idx, int pos, int &r, int &c, int &len) {
 GZ_HD uint32_t line_word(const uint32_t *m8, int idx) {
     int r, c, len;
     line_cell(idx, 0, r, c, len);
+    if (idx < 15) return (m8[r >> 1] >> ((r & 1) * 16)) & 0x7FFFu;   // a row is half a word
+    // consecutive cells of a line are a constant bit distance apart: 16 (column), 17 (diagonal), 15 (anti-diagonal)
+    const int step = idx < 30 ? 16 : idx < 59 ? 17 : 15;
+    int p = (r << 4) | c;
     uint32_t out = 0;
-    for (int pos = 0; pos < len; ++pos) {
-        line_cell(idx, pos, r, c, len);
-        int p = (r << 4) | c;
-        out |= ((m8[p >> 5] >> (p & 31)) & 1u) << pos;
-    }
+    for (int pos = 0; pos < len; ++pos, p += step) out |= ((m8[p >> 5] >> (p & 31)) & 1u) << pos;
     return out;
 }
 
