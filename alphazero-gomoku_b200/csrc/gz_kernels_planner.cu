@@ -65,20 +65,27 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
                     : kNoScore;
         if (scores2 && (p >> 4) < 15 && (p & 15) < 15) scores2[(size_t)g * kCells + bit_to_cell(p)] = sc[i];
     }
-    // stable descending top-k: k rounds of (max score, smallest position)
+    // stable descending top-k: k rounds of (max score, smallest position).  Scores fit 31 bits (|score| < 2^30:
+    // at most 2 * pattern score + 6, or the +-2e6 / -2e5 sentinels), so a round is a per-lane maximum over its
+    // 8 cells and two warp-wide redux.max: the biased score, then 255 - position among the lanes that hold it.
+    uint32_t key[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) key[i] = sc[i] != kNoScore ? (uint32_t)(sc[i] + (1ll << 30)) : 0u;
     int n = 0;
     for (int j = 0; j < k; ++j) {
-        long long best = kNoScore;
-        int bi = -1;
+        uint32_t lhi = 0u;
+        int li = 0;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-            if (sc[i] != kNoScore && (bi < 0 || sc[i] > best)) { best = sc[i]; bi = 32 * i + lane; }
-        warp_argmax_first_ll(best, bi);
-        if (bi < 0) break;
+            if (key[i] > lhi) { lhi = key[i]; li = i; }      // strict: the lane's smallest position wins ties
+        const uint32_t mhi = __reduce_max_sync(0xffffffffu, lhi);
+        if (mhi == 0u) break;
+        const uint32_t mlo = __reduce_max_sync(0xffffffffu, lhi == mhi ? 255u - (uint32_t)(32 * li + lane) : 0u);
+        const int bi = 255 - (int)mlo;
         if ((bi & 31) == lane) {
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                if (i == (bi >> 5)) sc[i] = kNoScore;
+                if (i == (bi >> 5)) key[i] = 0u;
         }
         if (lane == 0) topk[g * kMaxTopK + j] = bit_to_cell(bi);
         ++n;
