@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libgomoku_b200.so")
 SOURCES = ["gz_api.cu", "gz_kernels_board.cu", "gz_kernels_rollout.cu", "gz_kernels_planner.cu",
-           "gz_kernels_tree.cu", "gz_kernels_selfplay.cu", "gz_nn_fp32.cu", "gz_nn_bf16.cu", "gz_nn_fc.cu"]
+           "gz_kernels_tree.cu", "gz_kernels_selfplay.cu", "gz_kernels_dataset.cu", "gz_nn_fp32.cu", "gz_nn_bf16.cu", "gz_nn_fc.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-fmad=true", "-cudart", "static"]
 FLAGS += os.environ.get("GZ_EXTRA_NVCC_FLAGS", "").split()   # e.g. -DGZ_HEAD_TIMING: per-phase clock64 printf

@@ -759,6 +759,27 @@ extern "C" int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t
     return GZ_OK;
 }
 
+// ---- dataset build -----------------------------------------------------------------------------------
+extern "C" int gz_dataset_build(gz_handle h, const gz_replay_record *d_records, int64_t n, const int32_t *d_chosen,
+                                int64_t m, const int64_t *d_sample_ids, int64_t first, int64_t count,
+                                int32_t reference_exact, float *d_planes, int64_t *d_move, float *d_value,
+                                void *stream) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_dataset_build: null handle");
+    if (n < 0 || m < 0 || count < 0 || first < 0) return fail(GZ_ERR_ARG, "gz_dataset_build: negative size");
+    if (count == 0) return GZ_OK;
+    if (!d_records || !d_planes || !d_move || !d_value) return fail(GZ_ERR_ARG, "gz_dataset_build: null pointer");
+    if (m > 0 && !d_chosen) return fail(GZ_ERR_ARG, "gz_dataset_build: m > 0 without d_chosen");
+    if (!d_sample_ids && first + count > n + 8 * m) return fail(GZ_ERR_ARG, "gz_dataset_build: range past n + 8 m");
+    if (count > (1ll << 26)) return fail(GZ_ERR_ARG, "gz_dataset_build: more than 2^26 samples in one call");
+    CK(cudaSetDevice(e->cfg.device));
+    launch_dataset_build(d_records, n, d_chosen, m, reinterpret_cast<const long long *>(d_sample_ids), first, count,
+                         reference_exact != 0, d_planes, reinterpret_cast<long long *>(d_move), d_value, strm(stream));
+    e->launches += 1;
+    CKL();
+    return GZ_OK;
+}
+
 // ---- self-play -----------------------------------------------------------------------------------
 static void sp_free(Engine *e) {
     void *ptrs[] = {e->sp.boards, e->sp.ai, e->sp.best, e->sp.game_id, e->sp.generation, e->sp.staging,

@@ -230,6 +230,9 @@ void launch_tree_finalize(const Engine &e, int G, const SearchCfg &c, int32_t *c
 
 // self-play kernels (gz_kernels_selfplay.cu)
 void launch_sp_begin(const SelfPlayArrays &sp, int G, const SelfPlayCfg &c, cudaStream_t s);
+void launch_dataset_build(const gz_replay_record *records, long long n, const int32_t *chosen, long long m,
+                          const long long *sample_ids, long long first, long long count, bool reference_exact,
+                          float *planes, long long *move, float *value, cudaStream_t s);
 void launch_sp_apply(const SelfPlayArrays &sp, int G, const SelfPlayCfg &c, cudaStream_t s);
 
 // networks, fp32 path (gz_nn_fp32.cu)

@@ -18,6 +18,7 @@
 //   warp 1    single-thread tcgen05.mma issuer; accumulators double buffered in TMEM
 //   warps 2-5 epilogue: tcgen05.ld, bias (+ residual) + ReLU, zero the padding positions, pack to
 //             bf16, 16-byte coalesced stores
+#include <cstdlib>
 #include "gz_engine.h"
 #include "gz_tcgen05.cuh"
 
@@ -572,6 +573,8 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
         configured = true;
     }
     int grid = G < e.sm_count ? G : e.sm_count;
+    static const int cap = getenv("GZ_CONV_GRID") ? atoi(getenv("GZ_CONV_GRID")) : 0;   // EXPERIMENT
+    if (cap > 0 && grid > cap) grid = cap;
     kern<<<grid, 192, C::SMEM, s>>>(in, w, bias, res, out, active, G, heads);
 }
 

@@ -23,6 +23,7 @@ EXPORTS = [
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
     "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_set_lanes", "gz_get_stage_times", "gz_debug_pv_layer",
     "gz_selfplay_begin", "gz_selfplay_step", "gz_selfplay_drain", "gz_selfplay_boards", "gz_selfplay_get_stats",
+    "gz_dataset_build",
 ]
 
 STAGES = ["tree", "pv_conv0", "pv_tower", "pv_heads", "planner_score", "gn_convs", "gn_head", "dqn",
@@ -310,6 +311,38 @@ class Engine:
         out = t.empty((max(st["records_ready"], 1), REPLAY_DTYPE.itemsize), dtype=t.uint8, device=self.device)
         self._ck(self.L.gz_selfplay_drain(self.h, _ptr(out), C.c_int64(out.shape[0]), C.byref(n), self._stream()))
         return out[:n.value]
+
+    def dataset_build(self, records, chosen=None, sample_ids=None, first=0, count=None, reference_exact=True):
+        """gz_dataset_build: (planes f32 [count,3,15,15], move i64 [count], value f32 [count]) device tensors
+        from packed replay records (uint8 device tensor [n, 72]); `chosen` = the records augmented eightfold."""
+        t = self.torch
+        rec = records if t.is_tensor(records) else t.as_tensor(np.ascontiguousarray(records).view(np.uint8))
+        rec = rec.to(self.device).contiguous().view(t.uint8).reshape(-1, REPLAY_DTYPE.itemsize)
+        n = rec.shape[0]
+        if chosen is None:
+            ch = t.zeros(0, dtype=t.int32)
+        elif t.is_tensor(chosen):
+            ch = chosen.to(t.int32)
+        else:
+            ch = t.as_tensor(np.asarray(chosen, np.int32))
+        ch = ch.to(self.device).contiguous()
+        m = ch.shape[0]
+        ids = None
+        if sample_ids is not None:
+            ids = sample_ids.to(t.int64) if t.is_tensor(sample_ids) else t.as_tensor(np.asarray(sample_ids, np.int64))
+            ids = ids.to(self.device).contiguous()
+            count = ids.shape[0]
+        elif count is None:
+            count = n + 8 * m - first
+        planes = t.empty((count, 3, 15, 15), dtype=t.float32, device=self.device)
+        move = t.empty(count, dtype=t.int64, device=self.device)
+        value = t.empty(count, dtype=t.float32, device=self.device)
+        self._ck(self.L.gz_dataset_build(self.h, _ptr(rec) if n else None, C.c_int64(n), _ptr(ch) if m else None,
+                                         C.c_int64(m), _ptr(ids) if ids is not None else None, C.c_int64(first),
+                                         C.c_int64(count), int(bool(reference_exact)), _ptr(planes) if count else None,
+                                         _ptr(move) if count else None, _ptr(value) if count else None,
+                                         self._stream()))
+        return planes, move, value
 
     def selfplay_boards(self):
         out = self.torch.empty((self._sp_games, BOARD_BYTES), dtype=self.torch.uint8, device=self.device)

@@ -111,3 +111,45 @@ def gather_replay(records, group=None):
     parts = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(parts, pad, group=group)
     return torch.cat([p[:k] for p, k in zip(parts, sizes)], dim=0)
+
+
+class GomokuSelfPlayDataset:
+    """GomokuSelfPlayDataset (training.py:104-134) decoded on the device from packed replay records.
+
+    Same constructor logic as the reference: every record once, plus the 8 symmetries (augment_sample,
+    training.py:63-70) of `max(1, int(n * augment_ratio))` records picked by `random.sample(range(n), k)` --
+    `rng` defaults to Python's global `random`, so a seeded run picks what the reference picks.
+    `reference_exact=True` keeps the reference's index transform as written (it turns the policy label the other
+    way round from the planes for odd quarter turns); False labels the cell the stone lands on.
+    Samples are decoded by gz_dataset_build: the whole set once (`materialize=True`: tensors .planes, .move,
+    .value and the reference's __getitem__) or batch by batch with `batch(sample_ids)`."""
+
+    def __init__(self, records, engine, use_augmentation=True, augment_ratio=0.5, rng=None, reference_exact=True,
+                 materialize=True):
+        import random as _random
+        self.engine, self.reference_exact = engine, bool(reference_exact)
+        self.records = records
+        self.n = int(records.shape[0]) if hasattr(records, "shape") else len(records)
+        self.chosen = []
+        if use_augmentation and self.n > 0:
+            aug_count = int(self.n * augment_ratio)
+            self.chosen = (rng or _random).sample(list(range(self.n)), k=max(1, aug_count))
+        self.planes = self.move = self.value = None
+        if materialize:
+            self.planes, self.move, self.value = engine.dataset_build(records, self.chosen,
+                                                                      reference_exact=self.reference_exact)
+
+    def __len__(self):
+        return self.n + 8 * len(self.chosen)
+
+    def batch(self, sample_ids):
+        """(planes [B,3,15,15], move [B], value [B,1]) for the given sample indices, decoded on demand."""
+        x, y, v = self.engine.dataset_build(self.records, self.chosen, sample_ids=sample_ids,
+                                            reference_exact=self.reference_exact)
+        return x, y, v.reshape(-1, 1)
+
+    def __getitem__(self, idx):
+        if self.planes is None:
+            x, y, v = self.batch([int(idx)])
+            return x[0], y[0], v[0]
+        return self.planes[idx], self.move[idx], self.value[idx].reshape(1)

@@ -407,6 +407,127 @@ def run_selfplay(args):
         dist.destroy_process_group()
 
 
+def synthetic_records(n, seed):
+    """n packed replay records (72 B) of random mid-game positions, vectorised: stone k of a random permutation
+    of the cells goes to colour k & 1, the record's move is the next cell of the permutation."""
+    import engine
+    rng = np.random.default_rng(seed)
+    rec = np.zeros(n, dtype=engine.REPLAY_DTYPE)
+    order = np.argsort(rng.random((n, 225)), axis=1).astype(np.int64)
+    k = rng.integers(0, 150, n)
+    rank = np.empty_like(order)
+    np.put_along_axis(rank, order, np.broadcast_to(np.arange(225), (n, 225)), axis=1)    # rank[i, cell]
+    bitpos = 16 * (np.arange(225) // 15) + np.arange(225) % 15
+    for colour in (0, 1):
+        on = (rank < k[:, None]) & ((rank & 1) == colour)
+        bits = np.zeros((n, 256), np.uint8)
+        bits[:, bitpos] = on
+        rec["stones"][:, colour] = np.packbits(bits, axis=1, bitorder="little").view("<u4").reshape(n, 8)
+    rec["move"] = order[np.arange(n), k]
+    rec["mover"] = 1 + (k & 1)
+    rec["outcome"] = rng.integers(-1, 2, n)
+    rec["ply"] = k
+    rec["game_id"] = np.arange(n)
+    return rec.view(np.uint8).reshape(n, 72)
+
+
+def run_dataset(args):
+    """GomokuSelfPlayDataset build (every record + 8 symmetries of 35 % of them, the ratio
+    training.py:461 uses) from --records packed replay records per GPU.  A step decodes the whole dataset
+    (n + 8 * int(0.35 n) samples of 2712 B) into device tensors; records are resident in HBM for `value`,
+    come from pinned host memory for `e2e` (labels read back, planes stay on the device for the optimiser)."""
+    import random
+    import torch
+    import engine
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    n = args.records
+    eng = engine.Engine(max_games=8, max_simulations=4, device=local)
+    rec_h = torch.from_numpy(synthetic_records(n, 99 + rank)).pin_memory()
+    random.seed(1234 + rank)
+    chosen = np.asarray(random.sample(range(n), k=max(1, int(n * 0.35))), np.int32)
+    count = n + 8 * len(chosen)
+    rec_d, ch_d = rec_h.cuda(), torch.from_numpy(chosen).cuda()
+    out = None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        out = eng.dataset_build(rec_d, ch_d, reference_exact=True)
+    barrier()
+    eng.reset_counters()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        del out
+        out = eng.dataset_build(rec_d, ch_d, reference_exact=True)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.finish()
+    launches = eng.counters()["kernel_launches"]
+    ch_h = torch.from_numpy(chosen).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        del out
+        out = eng.dataset_build(rec_h.cuda(non_blocking=True), ch_h.cuda(non_blocking=True), reference_exact=True)
+        labels = (out[1].cpu(), out[2].cpu())
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        peaks = load_peaks()
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle as orc
+        import selfplay
+        ns = min(n, 2048)
+        x, mv, _m, oc = selfplay.records_to_samples(rec_h.numpy()[:ns])
+        t1 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t1 < min(args.cpu_seconds, 10.0):
+            ox, _, _ = orc.dataset_samples(x, mv, oc, list(range(0, ns, 3)), reference_exact=True)
+            reps += 1
+        cpu_rate = reps * len(ox) / (time.perf_counter() - t1)
+        per_sample = 675 * 4 + 8 + 4            # written
+        bytes_step = count * per_sample + n * 72 + len(chosen) * 4
+        gbs = bytes_step * args.steps / (t[0].item() / 1e3) / 1e9
+        print(json.dumps({
+            "metric": "dataset_samples_per_sec", "value": world * count * args.steps / (t[0].item() / 1e3),
+            "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": t[0].item() / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32 bitboards -> f32", "data": "synthetic",
+            "config": {"workload": "GomokuSelfPlayDataset build: %d records per GPU, augment_ratio 0.35 -> %d samples "
+                                   "(training.py:104-134), reference_exact index transform" % (n, count),
+                       "records_per_gpu": n, "samples_per_gpu": count,
+                       "l2_policy": "output (%.1f GB per step) exceeds the 126 MB L2" % (count * per_sample / 1e9)},
+            "clocks": clocks,
+            "e2e": {"value": world * count * args.steps / (t[1].item() / 1e3), "unit": "samples/s",
+                    "h2d_bytes_per_step": n * 72 + len(chosen) * 4, "d2h_bytes_per_step": count * 12},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s",
+                         "frac": gbs / peaks["hbm"], "traffic": None, "kernel": "k_dataset_build",
+                         "algorithmic_bytes_per_sample": per_sample, "peak_source": peaks["source"] + " (copy)"},
+            "cpu_baseline": {"value": cpu_rate, "unit": "samples/s", "cores": 1, "kind": "port",
+                             "sample": "numpy restatement (oracle.dataset_samples) on %d records, %d passes" % (ns, reps)}}))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -419,13 +540,17 @@ def main():
                     help="independent game groups advanced on separate CUDA streams (0 = engine default)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
                     help="network arithmetic: bf16 tcgen05 (timed mode) or fp32 FFMA (parity mode)")
-    ap.add_argument("--mode", default="search", choices=["search", "selfplay"],
-                    help="search: sims/s on fixed positions (the headline); selfplay: games/hour")
+    ap.add_argument("--mode", default="search", choices=["search", "selfplay", "dataset"],
+                    help="search: sims/s on fixed positions (the headline); selfplay: games/hour; "
+                         "dataset: training samples/s of the dataset build (SURVEY 8f row 2)")
+    ap.add_argument("--records", type=int, default=1 << 20, help="dataset mode: replay records per GPU")
     ap.add_argument("--min-games", type=int, default=4096, help="selfplay mode: games to finish per rank")
     ap.add_argument("--max-plies", type=int, default=2000)
     args = ap.parse_args()
     if args.mode == "selfplay" and args.impl != "reference":
         return run_selfplay(args)
+    if args.mode == "dataset" and args.impl != "reference":
+        return run_dataset(args)
     if args.impl == "reference":
         run_reference(args)
     else:

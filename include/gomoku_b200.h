@@ -240,6 +240,25 @@ int gz_selfplay_drain(gz_handle h, gz_replay_record *d_out, int64_t cap, int64_t
 int gz_selfplay_boards(gz_handle h, gz_board *d_out, void *stream);
 int gz_selfplay_get_stats(gz_handle h, gz_selfplay_stats *out);
 
+/* ---- dataset build ------------------------------------------------------------ */
+/* GomokuSelfPlayDataset + augment_sample (training.py:104-134, 38-70): training samples from packed replay
+ * records, decoded on the device.  The virtual dataset has n + 8*m samples:
+ *   sample i < n                : record i as recorded;
+ *   sample n + 8*j + 2*k + f    : record d_chosen[j] under symmetry (k quarter turns, then a horizontal flip when
+ *                                 f = 1), in the order augment_sample emits them (k = 0..3, f = 0, 1).
+ * Which records are augmented (random.sample over range(n), training.py:118-119) is the caller's choice.
+ * Emits `count` samples: ids d_sample_ids[0..count) when given, else first .. first + count - 1.
+ *   d_planes  f32 [count][3][15][15]  black, white, empty (GomokuBoard.get_board_tensor), transformed as
+ *                                     _transform_planes does: np.rot90 counter-clockwise k times, then np.flip(axis=2)
+ *   d_move    i64 [count]             the played move's index under _transform_index
+ *   d_value   f32 [count]             the record's outcome (+1 / -1 / 0 from the mover's point of view)
+ * reference_exact != 0 reproduces _transform_index as written: it turns the index CLOCKWISE while the planes turn
+ * counter-clockwise, so for k = 1, 3 the label does not point at the played stone (probed);
+ * reference_exact = 0 turns the index with the planes. */
+int gz_dataset_build(gz_handle h, const gz_replay_record *d_records, int64_t n, const int32_t *d_chosen,
+                     int64_t m, const int64_t *d_sample_ids, int64_t first, int64_t count,
+                     int32_t reference_exact, float *d_planes, int64_t *d_move, float *d_value, void *stream);
+
 /* ---- stage timing ---------------------------------------------------------------------------------- */
 /* CUDA-event timing of the engine's kernel groups on the launching stream.  When enabled, every
  * group of launches inside gz_search / gz_rollout / gz_pv_forward / ... is bracketed by two events;

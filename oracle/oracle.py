@@ -208,3 +208,47 @@ class Oracle:
                           C.byref(st))
         k = st.n_nodes
         return dict(parent=parent[:k], move=move[:k], visits=visits[:k], value=value[:k], stats=st)
+
+
+# ---- dataset build: CPU restatement of training.py:38-70,104-134 (numpy; test infrastructure) -------------------
+def transform_planes(planes, k_rot, flip):
+    """_transform_planes (training.py:44-51): np.rot90 counter-clockwise k times over axes (1, 2), then np.flip(axis=2)."""
+    x = np.asarray(planes)
+    for _ in range(k_rot % 4):
+        x = np.rot90(x, k=1, axes=(1, 2))
+    if flip:
+        x = np.flip(x, axis=2)
+    return np.ascontiguousarray(x)
+
+
+def transform_index(idx, k_rot, flip, n=15, reference_exact=True):
+    """_transform_index (training.py:53-61) as written -- (r, c) -> (c, n-1-r) per quarter turn, i.e. CLOCKWISE,
+    against the planes' counter-clockwise turn -- or, with reference_exact=False, the index of the cell the
+    stone really lands on under transform_planes: (r, c) -> (n-1-c, r)."""
+    r, c = divmod(int(idx), n)
+    for _ in range(k_rot % 4):
+        r, c = (c, n - 1 - r) if reference_exact else (n - 1 - c, r)
+    if flip:
+        c = n - 1 - c
+    return r * n + c
+
+
+def augment_sample(planes, move_idx, reference_exact=True):
+    """augment_sample (training.py:63-70): the 8 symmetries in the order k_rot = 0..3, flip = False, True."""
+    return [(transform_planes(planes, k, f), transform_index(move_idx, k, f, reference_exact=reference_exact))
+            for k in range(4) for f in (False, True)]
+
+
+def dataset_samples(planes, moves, outcomes, chosen, reference_exact=True):
+    """GomokuSelfPlayDataset.__init__ (training.py:104-127) for a given choice of augmented records:
+    every record once, then 8 symmetries of each chosen record.  Returns (planes [N,3,15,15] f32, move [N] i64,
+    value [N] f32)."""
+    xs, ys, vs = [], [], []
+    for i in range(len(moves)):
+        xs.append(np.asarray(planes[i], np.float32)); ys.append(int(moves[i])); vs.append(float(outcomes[i]))
+    for i in chosen:
+        for x, y in augment_sample(planes[i], moves[i], reference_exact):
+            xs.append(np.asarray(x, np.float32)); ys.append(y); vs.append(float(outcomes[i]))
+    if not xs:
+        return np.zeros((0, 3, 15, 15), np.float32), np.zeros(0, np.int64), np.zeros(0, np.float32)
+    return np.stack(xs), np.asarray(ys, np.int64), np.asarray(vs, np.float32)

@@ -18,6 +18,7 @@ Parts (each -> tests/golden/<part>.npz):
   nets      logits / value / softmax of the three networks (fp32, 1 thread)   neural_network.py:132-159,214-252
   mctsb     DET-B playouts and searches (planner_steps>0)
   stoch     outcome frequencies of real-RNG playouts (Mersenne Twister)
+  dataset   SimpleReplay -> GomokuSelfPlayDataset with the 8-fold augmentation   training.py:38-134
 """
 import argparse
 import os
@@ -608,8 +609,67 @@ def part_stoch(pool, outdir):
     print("stoch:", len(merged))
 
 
+# ----------------------------------------------------------------------------- part: dataset
+def part_dataset(pool, outdir):
+    """training.py:77-134 run as shipped: a SimpleReplay filled ply by ply from the shared position list (every
+    sequence = one game: planes before the move, move index, mover), finalize_with_winner, then
+    GomokuSelfPlayDataset(replay, True, 0.35) under random.seed(1234).  random.sample is wrapped only to record
+    which records it chose.  Planes are saved as uint8 (they are 0/1)."""
+    import training
+    seqs, _tags = load_positions(outdir)
+    stones, move, mover, outcome, ply, gid = [], [], [], [], [], []
+    states, out_moves, out_values, chosen_all, n_all = [], [], [], [], []
+    for g, seq in enumerate(seqs[:40:3] + seqs[-6:]):
+        seq = seq[:60]
+        board = gomoku_board.GomokuBoard()
+        replay = training.SimpleReplay()
+        for k, mv in enumerate(seq):
+            if board.game_over:
+                break
+            r, c = divmod(mv, 15)
+            cells = np.array(board.board, dtype=np.uint8).reshape(225)
+            bits = np.zeros((2, 256), np.uint8)
+            for colour in (1, 2):
+                rr, cc = np.nonzero(cells.reshape(15, 15) == colour)
+                bits[colour - 1, 16 * rr + cc] = 1
+            stones.append(np.packbits(bits, axis=1, bitorder="little").view("<u4").reshape(2, 8))
+            replay.add(board.get_board_tensor(), mv, board.current_player)
+            move.append(mv); mover.append(board.current_player); ply.append(k); gid.append(g)
+            assert board.make_move(r, c)
+        winner = board.winner if board.game_over else (None if g % 3 else 1 + g % 2)   # unfinished: mix of labels
+        replay.finalize_with_winner(winner)
+        outcome.extend(replay.outcomes)
+        picked = []
+        real_sample = random.sample
+        def recording_sample(population, k):   # noqa: E306
+            out = real_sample(population, k)
+            picked.append(list(out))
+            return out
+        random.seed(1234 + g)
+        random.sample = recording_sample
+        try:
+            ds = training.GomokuSelfPlayDataset(replay, use_augmentation=True, augment_ratio=0.35)
+        finally:
+            random.sample = real_sample
+        states.append(np.stack([x for x, _, _ in ds.samples]).astype(np.uint8))
+        out_moves.append(np.array([y for _, y, _ in ds.samples], np.int64))
+        out_values.append(np.array([v for _, _, v in ds.samples], np.float32))
+        chosen_all.append(np.array(picked[0], np.int32)); n_all.append(len(replay))
+    rec = np.zeros(len(move), dtype=[("stones", "<u4", (2, 8)), ("move", "u1"), ("mover", "u1"), ("outcome", "i1"),
+                                     ("ply", "u1"), ("game_id", "<u4")])
+    rec["stones"] = np.stack(stones); rec["move"] = move; rec["mover"] = mover; rec["outcome"] = outcome
+    rec["ply"] = ply; rec["game_id"] = gid
+    np.savez_compressed(os.path.join(outdir, "dataset.npz"), records=rec.view(np.uint8).reshape(len(move), 72),
+                        game_n=np.array(n_all, np.int32), chosen=np.concatenate(chosen_all),
+                        chosen_n=np.array([len(c) for c in chosen_all], np.int32),
+                        planes=np.concatenate(states), move=np.concatenate(out_moves),
+                        value=np.concatenate(out_values))
+    print("dataset: %d games, %d records, %d samples" % (len(n_all), len(move), sum(len(x) for x in out_moves)))
+
+
 PARTS = dict(positions=part_positions, boards=part_boards, tiers=part_tiers, rollout=part_rollout,
-             mcts=part_mcts, planner=part_planner, nets=part_nets, mctsb=part_mctsb, stoch=part_stoch)
+             mcts=part_mcts, planner=part_planner, nets=part_nets, mctsb=part_mctsb, stoch=part_stoch,
+             dataset=part_dataset)
 
 
 def main():
