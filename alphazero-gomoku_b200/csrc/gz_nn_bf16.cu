@@ -62,8 +62,13 @@ __device__ __forceinline__ void store_head_operand(uint8_t *tile_base, int board
     *reinterpret_cast<uint16_t *>(dst + kHeadBlockBytes) = (uint16_t)(ptx::pack_bf16(r, 0.f) & 0xFFFFu);
 }
 
+// Epilogue warps: 4 (each does both halves of the board) when the 144 UMMAs of a 128 -> 128 layer hide the
+// epilogue anyway; 8 (one half each) for the 3 -> C input convolutions, whose 18 UMMAs per board leave the
+// kernel waiting for TMEM loads and stores (3.4 TB/s of output with 4 warps).
+template <bool FROM_BOARD> __host__ __device__ constexpr int conv_epi_warps() { return FROM_BOARD ? 8 : 4; }
+
 template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false, bool HEADS = false>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(64 + 32 * conv_epi_warps<FROM_BOARD>(), 1)
 k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w_packed,
             const float *__restrict__ bias, const uint8_t *__restrict__ res_planes,
             uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G, HeadConv heads) {
@@ -89,7 +94,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             ptx::mbar_init(&a_full[i], 1);
             ptx::mbar_init(&a_empty[i], 1);
             ptx::mbar_init(&acc_full[i], 1);
-            ptx::mbar_init(&acc_empty[i], 4);
+            ptx::mbar_init(&acc_empty[i], conv_epi_warps<FROM_BOARD>());
         }
         for (int i = 0; i < 4; ++i) {
             ptx::mbar_init(&b_full[i], 1);
@@ -116,11 +121,20 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             ptx::mbar_expect_tx(&b_full[0], C::KSTEPS * C::WSTEP_BYTES);
             ptx::bulk_g2s(wbuf, w_packed, C::KSTEPS * C::WSTEP_BYTES, &b_full[0]);
         }
+        // the next board's bitboards are fetched while this one is expanded (the loop is otherwise one global
+        // load latency per board long)
+        auto next_board = [&](int b) {
+            for (b += gridDim.x; b < G && active && !active[b]; b += gridDim.x) {}
+            return b;
+        };
+        auto load_stones = [&](int b) { return lane < 16 && b < G ? boards[b].stones[lane >> 3][lane & 7] : 0u; };
         uint32_t it = 0;
-        for (int b = blockIdx.x; b < G; b += gridDim.x) {
-            if (active && !active[b]) continue;
+        int b = blockIdx.x < G && active && !active[blockIdx.x] ? next_board(blockIdx.x) : blockIdx.x;
+        uint32_t st = load_stones(b);
+        while (b < G) {
             const int ab = it & 1;
-            const uint32_t st = lane < 16 ? boards[b].stones[lane >> 3][lane & 7] : 0u;
+            const int bn = next_board(b);
+            const uint32_t st_next = load_stones(bn);
             if (lane == 0) ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
             __syncwarp();
             uint8_t *dst = slab + ab * C::SLAB_BYTES;
@@ -140,6 +154,8 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&a_full[ab]);
             ++it;
+            b = bn;
+            st = st_next;
         }
     } else if (warp == 0) {
         // ================= producer =================
@@ -296,10 +312,14 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             const int bn = next_board(b);
             ptx::mbar_wait(&acc_full[ab], (it >> 1) & 1);
             ptx::tc_fence_after();
-            if (RESIDUAL) fetch_res(b, 1, res[1]);
-            half(b, ab, 0, res[0]);
-            if (RESIDUAL && bn < G) fetch_res(bn, 0, res[0]);
-            half(b, ab, 1, res[1]);
+            if (conv_epi_warps<FROM_BOARD>() == 8) {
+                half(b, ab, (warp - 2) >> 2, res[0]);        // FROM_BOARD layers have no residual
+            } else {
+                if (RESIDUAL) fetch_res(b, 1, res[1]);
+                half(b, ab, 0, res[0]);
+                if (RESIDUAL && bn < G) fetch_res(bn, 0, res[0]);
+                half(b, ab, 1, res[1]);
+            }
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[ab]);
@@ -575,7 +595,7 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
     int grid = G < e.sm_count ? G : e.sm_count;
     static const int cap = getenv("GZ_CONV_GRID") ? atoi(getenv("GZ_CONV_GRID")) : 0;   // EXPERIMENT
     if (cap > 0 && grid > cap) grid = cap;
-    kern<<<grid, 192, C::SMEM, s>>>(in, w, bias, res, out, active, G, heads);
+    kern<<<grid, 64 + 32 * conv_epi_warps<FROM_BOARD>(), C::SMEM, s>>>(in, w, bias, res, out, active, G, heads);
 }
 
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
