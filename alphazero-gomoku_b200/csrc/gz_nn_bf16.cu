@@ -257,6 +257,27 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             const int pos = 16 + 128 * h + 32 * q + lane;
             const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
             const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + ab * 2 * COUT + h * COUT;
+            if (FROM_BOARD && COUT == 64) {   // epilogue-bound layer: 64 columns per TMEM round trip (41 -> 35 us; no gain at 128)
+#pragma unroll 1
+                for (int c64 = 0; c64 < COUT; c64 += 64) {
+                    float v[64];
+                    ptx::tmem_ld64(taddr + c64, v);
+#pragma unroll
+                    for (int c0 = 0; c0 < 64; c0 += 16) {
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float x0 = fmaxf(v[c0 + 2 * i] + sbias[c64 + c0 + 2 * i], 0.f);
+                            const float x1 = fmaxf(v[c0 + 2 * i + 1] + sbias[c64 + c0 + 2 * i + 1], 0.f);
+                            pk[i] = valid ? ptx::pack_bf16(x0, x1) : 0u;
+                        }
+                        const size_t o0 = obase + (size_t)((c64 + c0) / 8) * kPlaneBytes + (size_t)pos * 16;
+                        *reinterpret_cast<uint4 *>(out_planes + o0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        *reinterpret_cast<uint4 *>(out_planes + o0 + kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    }
+                }
+                return;
+            }
             float hp0 = 0.f, hp1 = 0.f, hv0 = 0.f;
             if (HEADS) { hp0 = s_hw[3 * COUT]; hp1 = s_hw[3 * COUT + 1]; hv0 = s_hw[3 * COUT + 2]; }
 #pragma unroll(RESIDUAL ? COUT / 16 : 1)

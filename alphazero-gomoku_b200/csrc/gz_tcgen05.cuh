@@ -146,6 +146,34 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// Four x16 loads in flight, then the wait: the ~200-cycle TMEM round trip is paid once per 64 columns instead of
+// once per 16.  The wait statements name the loaded registers as in/out operands so that nothing that uses them
+// can be scheduled ahead of the wait.
+__device__ __forceinline__ void tmem_ld64(uint32_t taddr, float *v) {
+    uint32_t r[64];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        uint32_t *q = r + 16 * g;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7]), "=r"(q[8]),
+              "=r"(q[9]), "=r"(q[10]), "=r"(q[11]), "=r"(q[12]), "=r"(q[13]), "=r"(q[14]), "=r"(q[15])
+            : "r"(taddr + 16 * g)
+            : "memory");
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        uint32_t *q = r + 16 * g;
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(q[0]), "+r"(q[1]), "+r"(q[2]), "+r"(q[3]), "+r"(q[4]), "+r"(q[5]), "+r"(q[6]), "+r"(q[7]),
+                       "+r"(q[8]), "+r"(q[9]), "+r"(q[10]), "+r"(q[11]), "+r"(q[12]), "+r"(q[13]), "+r"(q[14]), "+r"(q[15])
+                     :
+                     : "memory");
+    }
+#pragma unroll
+    for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(r[i]);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t *>(&h);
