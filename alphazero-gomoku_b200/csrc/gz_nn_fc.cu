@@ -12,6 +12,7 @@
 //   warp 0      weight producer (bulk async copies)
 //   warp 1      single-thread tcgen05.mma issuer, owns the TMEM allocation
 //   warps 2-5   layer-1 operand generator, then the three epilogues (one board row per thread)
+#include <cstdio>
 #include "gz_engine.h"
 #include "gz_bitboard.cuh"
 #include "gz_tcgen05.cuh"
@@ -70,6 +71,17 @@ __device__ __forceinline__ void store_rows_scalar(float *stage, int lane, const 
     for (int r = 0; r < 32; ++r) {
         float *dst = reinterpret_cast<float *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(row_ptr), r));
         if (dst && c0 + lane < ncols) dst[c0 + lane] = stage[r * kStageRow + lane];
+    }
+}
+// same, for rows that are `pitch` floats apart from `warp_base` (row r of the warp is live iff bit r of row_mask):
+// no pointer shuffles, the loop is a shared-memory load and a store per row
+__device__ __forceinline__ void store_rows_scalar_affine(float *stage, int lane, const float *vals, float *warp_base,
+                                                         int pitch, uint32_t row_mask, int c0, int ncols) {
+    stage_block(stage, lane, vals);
+    if (c0 + lane < ncols) {
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r)
+            if ((row_mask >> r) & 1u) warp_base[(size_t)r * pitch + c0 + lane] = stage[r * kStageRow + lane];
     }
 }
 
@@ -155,6 +167,9 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
         const int qd = warp & 3;                 // TMEM lane quadrant of this warp
         const int m = 32 * qd + lane;            // board row of this thread
         const int b = tile * 128 + m;
+#ifdef GZ_HEAD_TIMING
+        long long tq[8]; tq[0] = clock64();
+#endif
         // ---- 704-bit plane vector of the board: black | white | empty in raster order
         {
             uint32_t v[22];
@@ -177,6 +192,9 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
 #pragma unroll
             for (int i = 0; i < 22; ++i) vec[m * 22 + i] = v[i];
         }
+#ifdef GZ_HEAD_TIMING
+        tq[1] = clock64();
+#endif
         // ---- layer-1 operand chunks: byte kg of the vector -> 8 bf16 zeros/ones
         for (int c = 0; c < kL1Chunks; ++c) {
             const int ab = c & 1;
@@ -196,15 +214,22 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
             ptx::mbar_arrive(&a_full[ab]);
         }
         // ---- epilogues
+#ifdef GZ_HEAD_TIMING
+        tq[2] = clock64();
+#endif
         const uint32_t trow = tmem_base + ((uint32_t)(32 * qd) << 16);
         for (int layer = 0; layer < 3; ++layer) {
             ptx::mbar_wait(&d_full[layer], 0);
+#ifdef GZ_HEAD_TIMING
+            tq[3 + layer] = clock64();
+#endif
             ptx::tc_fence_after();
             const uint32_t tcol = trow + (layer == 1 ? kFcN : 0);
             const float *bs = sbias + layer * kFcN;
             if (layer == 2) {   // Q values: rows written coalesced through a staging tile (the A buffers are free now)
                 float *stage = reinterpret_cast<float *>(abuf) + (warp - 2) * 32 * kStageRow;
-                float *q_row = b < G ? q + (size_t)b * kCells : nullptr;
+                float *q_warp = q + (size_t)(tile * 128 + 32 * qd) * kCells;
+                const uint32_t rows = __ballot_sync(0xffffffffu, b < G);
 #pragma unroll 1
                 for (int c0 = 0; c0 < kFcN; c0 += 32) {
                     float v[32];
@@ -212,7 +237,7 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
                     ptx::tmem_ld16(tcol + c0 + 16, v + 16);
 #pragma unroll
                     for (int i = 0; i < 32; ++i) v[i] += bs[c0 + i];
-                    store_rows_scalar(stage, lane, v, q_row, c0, kCells);
+                    store_rows_scalar_affine(stage, lane, v, q_warp, kCells, rows, c0, kCells);
                 }
                 break;
             }
@@ -237,6 +262,12 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
                 ptx::mbar_arrive(a2_full);
             }
         }
+#ifdef GZ_HEAD_TIMING
+        tq[6] = clock64();
+        if (blockIdx.x == 0 && threadIdx.x == 64)
+            printf("dqn: vector %lld, L1 operands %lld, wait L1 %lld, epi1+wait L2 %lld, epi2+wait L3 %lld, epi3 %lld cycles\n",
+                   tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4], tq[6] - tq[5]);
+#endif
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -425,8 +456,7 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
         float legal_sum = 0.f;
         float *stage = stage_all + wq * 32 * kStageRow;
         float *pol_row = a.policy && live ? a.policy + (size_t)b * kPolicyPitch : nullptr;
-        float *lg_row = a.logits && live ? a.logits + (size_t)b * kCells : nullptr;
-        float *pb_row = a.probs && live ? a.probs + (size_t)b * kCells : nullptr;
+        const uint32_t live_rows = __ballot_sync(0xffffffffu, live);
 #pragma unroll 1
         for (int c0 = 0; c0 < 256; c0 += 32) {
             float v[32], pr[32];
@@ -439,8 +469,8 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
                 pr[j] = c0 + j < kCells ? fast_ex2((v[j] - mx) * kLog2e) * inv : 0.f;
                 if (PV && ((lbits >> j) & 1u)) legal_sum += pr[j];
             }
-            if (a.logits) store_rows_scalar(stage, lane, v, lg_row, c0, kCells);
-            if (a.probs) store_rows_scalar(stage, lane, pr, pb_row, c0, kCells);
+            if (a.logits) store_rows_scalar_affine(stage, lane, v, a.logits + (size_t)(tile * 128 + 32 * qd) * kCells, kCells, live_rows, c0, kCells);
+            if (a.probs) store_rows_scalar_affine(stage, lane, pr, a.probs + (size_t)(tile * 128 + 32 * qd) * kCells, kCells, live_rows, c0, kCells);
             if (a.policy) store_rows_vec(stage, lane, pr, pol_row, c0);
         }
 #ifdef GZ_HEAD_TIMING
