@@ -242,16 +242,17 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
                 break;
             }
 #pragma unroll 1
-            for (int c0 = 0; c0 < kFcN; c0 += 16) {
-                float v[16];
-                ptx::tmem_ld16(tcol + c0, v);
-                if (layer < 2) {
+            for (int c64 = 0; c64 < kFcN; c64 += 64) {      // hidden layers: bias + ReLU -> bf16 A operand of the next GEMM
+                float v[64];
+                ptx::tmem_ld64(tcol + c64, v);
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
                     uint32_t pk[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
-                        pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + bs[c0 + 2 * i], 0.f),
-                                               fmaxf(v[2 * i + 1] + bs[c0 + 2 * i + 1], 0.f));
-                    uint8_t *dst = a2 + (c0 / 8) * 128 * 16 + m * 16;
+                        pk[i] = ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + bs[c64 + c0 + 2 * i], 0.f),
+                                               fmaxf(v[c0 + 2 * i + 1] + bs[c64 + c0 + 2 * i + 1], 0.f));
+                    uint8_t *dst = a2 + ((c64 + c0) / 8) * 128 * 16 + m * 16;
                     *reinterpret_cast<uint4 *>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4 *>(dst + 128 * 16) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
@@ -428,19 +429,19 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
         constexpr float kLog2e = 1.4426950408889634f;
         float mx = -INFINITY, sum = 0.f;
 #pragma unroll 1
-        for (int c0 = 0; c0 < 240; c0 += 16) {
-            float v[16];
-            ptx::tmem_ld16(trow + c0, v);
+        for (int c64 = 0; c64 < 256; c64 += 64) {
+            float v[64];
+            ptx::tmem_ld64(trow + c64, v);
             float cm = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                v[j] = c0 + j < kCells ? v[j] + s_bp[c0 + j] : -INFINITY;
+            for (int j = 0; j < 64; ++j) {
+                v[j] = c64 + j < kCells ? v[j] + s_bp[c64 + j] : -INFINITY;
                 cm = fmaxf(cm, v[j]);
             }
             const float nm = fmaxf(mx, cm);
             float cs = 0.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) cs += fast_ex2((v[j] - nm) * kLog2e);
+            for (int j = 0; j < 64; ++j) cs += fast_ex2((v[j] - nm) * kLog2e);
             sum = sum * fast_ex2((mx - nm) * kLog2e) + cs;
             mx = nm;
         }
