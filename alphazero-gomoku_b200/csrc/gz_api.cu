@@ -789,8 +789,8 @@ static void sp_free(Engine *e) {
     e->sp_alloc_games = e->sp_alloc_out = 0;
 }
 
-extern "C" int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration,
-                                 int64_t replay_capacity, void *stream) {
+static int sp_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration, int64_t replay_capacity,
+                    int32_t arena, int32_t sims_b, int64_t games_total, int64_t ordinal_stride, void *stream) {
     Engine *e = eng(h);
     int rc = check_batch(e, G, "gz_selfplay_begin");
     if (rc) return rc;
@@ -817,7 +817,16 @@ extern "C" int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params 
     e->sp_cfg.seed_lo = (uint32_t)(p->seed & 0xFFFFFFFFull);
     e->sp_cfg.seed_hi = (uint32_t)(p->seed >> 32);
     e->sp_cfg.id_base = p->game_base;
-    e->sp_cfg.id_stride = 1u << 20;   // id = game_base + slot + generation * 2^20 (see gomoku_b200.h)
+    // self-play: id = game_base + slot + generation * 2^20; arena: id = game ordinal (see gomoku_b200.h)
+    e->sp_cfg.id_stride = arena ? (uint32_t)ordinal_stride : 1u << 20;
+    e->sp_cfg.arena = arena;
+    e->sp_cfg.games_total = games_total;
+    e->sp_cfg.sims_a = p->num_simulations;
+    e->sp_cfg.sims_b = sims_b > 0 ? sims_b : p->num_simulations;
+    if (arena && e->sp_cfg.sims_b > e->cfg.max_simulations)
+        return fail(GZ_ERR_ARG, "gz_arena_begin: sims_b exceeds max_simulations");
+    // the search runs max(sims_a, sims_b) waves; each position stops at its own budget (gz_board.reserved[0])
+    if (arena && e->sp_cfg.sims_b > e->sp_params.num_simulations) e->sp_params.num_simulations = e->sp_cfg.sims_b;
     e->sp_cfg.deterministic = p->deterministic;
     e->sp_cfg.exploration = exploration;
     e->sp_G = G;
@@ -825,6 +834,36 @@ extern "C" int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params 
     launch_sp_begin(e->sp, G, e->sp_cfg, s);
     e->launches += 1;
     CKL();
+    return GZ_OK;
+}
+
+extern "C" int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration,
+                                 int64_t replay_capacity, void *stream) {
+    return sp_begin(h, G, p, exploration, replay_capacity, 0, 0, 0, 0, stream);
+}
+
+extern "C" int gz_arena_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration, int32_t opponent,
+                              int32_t sims_b, int64_t games_total, int64_t ordinal_stride, int64_t replay_capacity,
+                              void *stream) {
+    if (opponent != GZ_ARENA_ENGINE && opponent != GZ_ARENA_RANDOM)
+        return fail(GZ_ERR_ARG, "gz_arena_begin: opponent must be GZ_ARENA_ENGINE or GZ_ARENA_RANDOM");
+    if (games_total < 1 || ordinal_stride < G || ordinal_stride > 0x7FFFFFFFll)
+        return fail(GZ_ERR_ARG, "gz_arena_begin: games_total >= 1 and G <= ordinal_stride < 2^31 required");
+    return sp_begin(h, G, p, exploration, replay_capacity, opponent, opponent == GZ_ARENA_ENGINE ? sims_b : 0,
+                    games_total, ordinal_stride, stream);
+}
+
+extern "C" int gz_arena_get_stats(gz_handle h, gz_arena_stats *out) {
+    Engine *e = eng(h);
+    if (!e || !out) return fail(GZ_ERR_ARG, "gz_arena_get_stats: null argument");
+    if (e->sp_G < 1 || e->sp_cfg.arena == 0) return fail(GZ_ERR_STATE, "gz_arena_get_stats: gz_arena_begin was not called");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    unsigned long long c[SP_NCTR];
+    CK(cudaMemcpy(c, e->sp.ctr, sizeof c, cudaMemcpyDeviceToHost));
+    out->games_finished = (int64_t)c[SP_GAMES]; out->wins = (int64_t)c[SP_A_WINS];
+    out->losses = (int64_t)c[SP_A_LOSSES]; out->draws = (int64_t)c[SP_DRAWS];
+    out->plies_played = (int64_t)c[SP_PLIES]; out->steps = e->sp_steps;
     return GZ_OK;
 }
 

@@ -115,7 +115,8 @@ constexpr int kMaxLanes = 4;
 
 // ---- self-play state (gz_kernels_selfplay.cu) ---------------------------------------------------
 constexpr int kMaxPlies = 200;     // a game ends at the 200th stone at the latest (gomoku_board.py:106)
-enum { SP_CURSOR = 0, SP_GAMES, SP_PLIES, SP_BLACK, SP_WHITE, SP_DRAWS, SP_DROPPED, SP_NCTR = 8 };
+enum { SP_CURSOR = 0, SP_GAMES, SP_PLIES, SP_BLACK, SP_WHITE, SP_DRAWS, SP_DROPPED, SP_A_WINS, SP_A_LOSSES,
+       SP_NCTR = 12 };
 struct SelfPlayArrays {
     gz_board *boards;            // [G] current positions
     uint8_t *ai;                 // [G] side to move = the searching AI's colour
@@ -130,6 +131,11 @@ struct SelfPlayArrays {
 struct SelfPlayCfg {
     uint32_t seed_lo, seed_hi, id_base, id_stride;
     int32_t deterministic;
+    // evaluation arena (training.py:221-270): 0 = plain self-play; GZ_ARENA_ENGINE / GZ_ARENA_RANDOM: side A's colour
+    // alternates with the game ordinal (= game id), games with ordinal >= games_total are played but not counted
+    int32_t arena;
+    long long games_total;
+    int32_t sims_a, sims_b;      // arena: simulations per search of side A / side B (evaluate_model overrides only B's)
     double exploration;
 };
 

@@ -45,27 +45,48 @@ __device__ __forceinline__ void sp_record(gz_replay_record *stage, const gz_boar
     r.game_id = game_id;
 }
 
-// lane 0: empty board, then the six opening-book plies (ai_agent.py:121-122,138-166)
-__device__ void sp_start_game(gz_board &b, gz_replay_record *stage, const SelfPlayCfg &c, uint32_t game_id) {
+// one opening-book ply (ai_agent.py:138-166)
+__device__ __forceinline__ int sp_book_bit(const BB &empty, int ply, const SelfPlayCfg &c, uint32_t game_id) {
+    if (ply == 0) return (7 << 4) | 7;
+    BB c3 = bb_and(empty, square_mask(1));
+    if (bb_any(c3)) return sp_choice(c3, c, game_id, ply, 0u);
+    BB c5 = bb_and(empty, square_mask(2));
+    return sp_choice(bb_any(c5) ? c5 : empty, c, game_id, ply, 0u);
+}
+
+// side A's colour in the arena: black in even game ordinals (training.py:232,237,266)
+__device__ __forceinline__ int sp_side_a(const SelfPlayCfg &c, uint32_t game_id) { return (game_id & 1u) ? 2 : 1; }
+__device__ __forceinline__ bool sp_counted(const SelfPlayCfg &c, uint32_t game_id) {
+    return c.arena == 0 || c.games_total <= 0 || (long long)game_id < c.games_total;
+}
+
+// lane 0: empty board, then every ply that needs no search: the six opening-book plies
+// (ai_agent.py:121-122,138-166); against the RandomAgent (training.py:225-228) its plies are uniform random from
+// the first stone on and the loop runs until side A is to move with six stones on the board.
+__device__ int sp_start_game(gz_board &b, gz_replay_record *stage, const SelfPlayCfg &c, uint32_t game_id) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) b.stones[0][i] = b.stones[1][i] = 0u;
     b.move_count = 0; b.to_move = 1; b.status = 0;
     b.reserved[0] = b.reserved[1] = b.reserved[2] = 0u;
-    for (int ply = 0; ply < 6 && b.status == 0; ++ply) {
+    const int side_a = sp_side_a(c, game_id);
+    int plies = 0;
+    while (b.status == 0) {
+        const int ply = b.move_count;
+        const bool random_ply = c.arena == GZ_ARENA_RANDOM && b.to_move != side_a;
+        if (!random_ply && ply >= 6) break;
         BB empty = bb_empty_cells(bb_load(b.stones[0]), bb_load(b.stones[1]));
-        int bit;
-        if (ply == 0) bit = (7 << 4) | 7;
-        else {
-            BB c3 = bb_and(empty, square_mask(1));
-            if (bb_any(c3)) bit = sp_choice(c3, c, game_id, ply, 0u);
-            else {
-                BB c5 = bb_and(empty, square_mask(2));
-                bit = sp_choice(bb_any(c5) ? c5 : empty, c, game_id, ply, 0u);
-            }
-        }
+        int bit = random_ply ? sp_choice(empty, c, game_id, ply, 3u) : sp_book_bit(empty, ply, c, game_id);
         sp_record(stage, b, bit, game_id);
         board_place(b, bit);
+        ++plies;
     }
+    return plies;
+}
+
+// arena: the side to move decides how many simulations this position gets (gz_board.reserved[0])
+__device__ __forceinline__ void sp_set_budget(gz_board &b, const SelfPlayCfg &c, uint32_t game_id) {
+    int n = c.arena == 0 ? 0 : (b.to_move == sp_side_a(c, game_id) ? c.sims_a : c.sims_b);
+    b.reserved[0] = (uint32_t)n;
 }
 
 __global__ void __launch_bounds__(128) k_sp_begin(SelfPlayArrays sp, int G, SelfPlayCfg c) {
@@ -74,10 +95,11 @@ __global__ void __launch_bounds__(128) k_sp_begin(SelfPlayArrays sp, int G, Self
     gz_board b;
     sp.generation[g] = 0;
     sp.game_id[g] = c.id_base + (uint32_t)g;
-    sp_start_game(b, sp.staging + (size_t)g * kMaxPlies, c, sp.game_id[g]);
+    int n = sp_start_game(b, sp.staging + (size_t)g * kMaxPlies, c, sp.game_id[g]);
+    sp_set_budget(b, c, sp.game_id[g]);
     sp.boards[g] = b;
     sp.ai[g] = b.to_move;
-    atomicAdd(&sp.ctr[SP_PLIES], 6ull);
+    if (sp_counted(c, sp.game_id[g])) atomicAdd(&sp.ctr[SP_PLIES], (unsigned long long)n);
 }
 
 __global__ void __launch_bounds__(128) k_sp_apply(SelfPlayArrays sp, int G, SelfPlayCfg c) {
@@ -85,7 +107,7 @@ __global__ void __launch_bounds__(128) k_sp_apply(SelfPlayArrays sp, int G, Self
     const int lane = threadIdx.x & 31;
     if (g >= G) return;
     gz_replay_record *stage = sp.staging + (size_t)g * kMaxPlies;
-    int finished = 0, n_plies = 0, winner = 0;
+    int finished = 0, n_plies = 0, winner = 0, counted = 0;
     gz_board b;
     if (lane == 0) {
         b = sp.boards[g];
@@ -97,13 +119,26 @@ __global__ void __launch_bounds__(128) k_sp_apply(SelfPlayArrays sp, int G, Self
         if (sp_random(c, gid, ply) < c.exploration) bit = sp_choice(empty, c, gid, ply, 2u);   // (:128-129)
         sp_record(stage, b, bit, gid);
         board_place(b, bit);
-        atomicAdd(&sp.ctr[SP_PLIES], 1ull);
+        int played = 1;
+        if (c.arena == GZ_ARENA_RANDOM && b.status == 0) {   // the RandomAgent's reply (training.py:225-228)
+            BB e2 = bb_empty_cells(bb_load(b.stones[0]), bb_load(b.stones[1]));
+            int rb = sp_choice(e2, c, gid, b.move_count, 3u);
+            sp_record(stage, b, rb, gid);
+            board_place(b, rb);
+            ++played;
+        }
+        counted = sp_counted(c, gid) ? 1 : 0;
+        if (counted) atomicAdd(&sp.ctr[SP_PLIES], (unsigned long long)played);
         if (b.status != 0) {
             finished = 1;
             n_plies = b.move_count;
             winner = b.status;
-            atomicAdd(&sp.ctr[SP_GAMES], 1ull);
-            atomicAdd(&sp.ctr[winner == 1 ? SP_BLACK : winner == 2 ? SP_WHITE : SP_DRAWS], 1ull);
+            if (counted) {
+                atomicAdd(&sp.ctr[SP_GAMES], 1ull);
+                atomicAdd(&sp.ctr[winner == 1 ? SP_BLACK : winner == 2 ? SP_WHITE : SP_DRAWS], 1ull);
+                if (c.arena != 0 && winner != 3)
+                    atomicAdd(&sp.ctr[winner == sp_side_a(c, gid) ? SP_A_WINS : SP_A_LOSSES], 1ull);
+            }
         }
     }
     finished = __shfl_sync(0xffffffffu, finished, 0);
@@ -111,7 +146,7 @@ __global__ void __launch_bounds__(128) k_sp_apply(SelfPlayArrays sp, int G, Self
         n_plies = __shfl_sync(0xffffffffu, n_plies, 0);
         winner = __shfl_sync(0xffffffffu, winner, 0);
         long long base = -1;
-        if (lane == 0) {
+        if (lane == 0 && counted) {
             unsigned long long old = atomicAdd(&sp.ctr[SP_CURSOR], (unsigned long long)n_plies);
             if ((long long)(old + n_plies) > sp.out_cap) {
                 atomicAdd(&sp.ctr[SP_CURSOR], (unsigned long long)(-(long long)n_plies));
@@ -139,11 +174,12 @@ __global__ void __launch_bounds__(128) k_sp_apply(SelfPlayArrays sp, int G, Self
             sp.generation[g] = gen;
             uint32_t gid = c.id_base + (uint32_t)g + gen * (uint32_t)c.id_stride;
             sp.game_id[g] = gid;
-            sp_start_game(b, stage, c, gid);
-            atomicAdd(&sp.ctr[SP_PLIES], 6ull);
+            int n = sp_start_game(b, stage, c, gid);
+            if (sp_counted(c, gid)) atomicAdd(&sp.ctr[SP_PLIES], (unsigned long long)n);
         }
     }
     if (lane == 0) {
+        sp_set_budget(b, c, sp.game_id[g]);
         sp.boards[g] = b;
         sp.ai[g] = b.to_move;
     }

@@ -113,6 +113,18 @@ __global__ void __launch_bounds__(128) k_tree_step(TreeArrays t, SimArrays sm, i
         __syncwarp();
     }
     if (sim >= c.S) return;   // the extra launch after the last simulation only backs up
+    // per-position budget (gz_board.sim_budget, 0 = c.S): a tree that has run its simulations idles for the
+    // rest of the search -- finished dummy leaf, nothing to evaluate, nothing to back up
+    const int bud = (int)t.root[g].reserved[0];
+    if (bud != 0 && sim >= bud) {
+        if (lane == 0) {
+            sm.board[g].status = 3;
+            sm.leaf[g] = -1;
+            sm.steps[g] = 0;
+            sm.need_eval[g] = 0;
+        }
+        return;
+    }
     int nn = t.n_nodes[g];
     // ---- select (:224-232)
     int cur = 0;

@@ -23,8 +23,10 @@ EXPORTS = [
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
     "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_set_lanes", "gz_get_stage_times", "gz_debug_pv_layer",
     "gz_selfplay_begin", "gz_selfplay_step", "gz_selfplay_drain", "gz_selfplay_boards", "gz_selfplay_get_stats",
-    "gz_dataset_build",
+    "gz_dataset_build", "gz_arena_begin", "gz_arena_get_stats",
 ]
+
+ARENA_ENGINE, ARENA_RANDOM = 1, 2     # GZ_ARENA_ENGINE / GZ_ARENA_RANDOM
 
 STAGES = ["tree", "pv_conv0", "pv_tower", "pv_heads", "planner_score", "gn_convs", "gn_head", "dqn",
           "planner_pick", "rollout_tail", "misc", "reserved"]
@@ -50,6 +52,10 @@ class GzCounters(C.Structure):
 class GzSelfplayStats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("games_finished", "plies_played", "black_wins", "white_wins", "draws",
                                           "records_ready", "records_dropped", "steps")]
+
+
+class GzArenaStats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("games_finished", "wins", "losses", "draws", "plies_played", "steps")]
 
 
 BOARD_BYTES = 80
@@ -294,6 +300,22 @@ class Engine:
         self._sp_games = int(n_games)
         self._ck(self.L.gz_selfplay_begin(self.h, int(n_games), C.byref(params), C.c_double(exploration),
                                           C.c_int64(replay_capacity), self._stream()))
+
+    def arena_begin(self, n_games, params, exploration, opponent, games_total, ordinal_stride=None,
+                    replay_capacity=0, sims_b=0):
+        """evaluate_model's game loop (training.py:221-270) for n_games concurrent games; opponent is ARENA_ENGINE
+        or ARENA_RANDOM; params.num_simulations is side A's budget, sims_b side B's (0 = the same).  Stepped /
+        drained with the selfplay_* calls."""
+        self._sp_games = int(n_games)
+        self._ck(self.L.gz_arena_begin(self.h, int(n_games), C.byref(params), C.c_double(exploration),
+                                       C.c_int32(opponent), C.c_int32(sims_b), C.c_int64(games_total),
+                                       C.c_int64(ordinal_stride or n_games), C.c_int64(replay_capacity),
+                                       self._stream()))
+
+    def arena_stats(self):
+        st = GzArenaStats()
+        self._ck(self.L.gz_arena_get_stats(self.h, C.byref(st)))
+        return {n: getattr(st, n) for n, _ in GzArenaStats._fields_}
 
     def selfplay_step(self):
         self._ck(self.L.gz_selfplay_step(self.h, self._stream()))

@@ -44,7 +44,8 @@ typedef struct {
     uint16_t move_count;   /* len(move_history) */
     uint8_t to_move;       /* current_player: 1 black, 2 white */
     uint8_t status;        /* 0 live, 1 black won, 2 white won, 3 draw (game_over, winner) */
-    uint32_t reserved[3];
+    uint32_t reserved[3];  /* [0]: simulation budget of this position inside gz_search, 0 = p->num_simulations (the
+                              arena sets it: side A and side B may search with different budgets); [1..2]: zero */
 } gz_board;
 
 typedef struct {
@@ -239,6 +240,35 @@ int gz_selfplay_drain(gz_handle h, gz_replay_record *d_out, int64_t cap, int64_t
 /* Current boards of the G games (device, for inspection) and the counters. */
 int gz_selfplay_boards(gz_handle h, gz_board *d_out, void *stream);
 int gz_selfplay_get_stats(gz_handle h, gz_selfplay_stats *out);
+
+/* ---- evaluation arena (training.py:221-270 evaluate_model) ------------------------------- */
+/* `games_total` evaluation games of side A against side B, G of them at a time, on the self-play machinery above
+ * (gz_selfplay_step plays one A ply of every game; gz_selfplay_drain / gz_selfplay_boards work unchanged).
+ * Game ordinals are global: slot s of this handle plays ordinals p->game_base + s + k * ordinal_stride, k = 0, 1, ...
+ * (ordinal_stride = G * number of ranks), and the ordinal is the record's game_id.  As in evaluate_model side A
+ * ("current") is BLACK in even ordinals and WHITE in odd ones (black_is_current toggles per game, :232,266).
+ *   GZ_ARENA_ENGINE  B is the same agent as A playing the other colour (the reference's `baseline` AlphaZeroGomokuAI;
+ *                    the two differ only in `.model`, which the search never reads -- SURVEY fact 3): both sides use
+ *                    the opening book for the first six stones, then the search with ai_player = the side to move,
+ *                    then the epsilon override.
+ *   GZ_ARENA_RANDOM  B is evaluate_model's RandomAgent (:225-228): random.choice over the legal moves, from the very
+ *                    first stone (no book, no epsilon).  B's reply is played in the same step as A's move, and B's
+ *                    plies before A's first searched move are played when the game starts, so every step still
+ *                    searches G positions with A to move.
+ * Games with ordinal >= games_total keep the slot busy but are neither counted nor recorded. */
+enum { GZ_ARENA_ENGINE = 1, GZ_ARENA_RANDOM = 2 };
+typedef struct {
+    int64_t games_finished;      /* counted games (ordinal < games_total) */
+    int64_t wins, losses, draws; /* from side A's point of view (training.py:258-264) */
+    int64_t plies_played, steps;
+} gz_arena_stats;
+/* p->num_simulations is side A's budget; sims_b (GZ_ARENA_ENGINE only, 0 = the same) is side B's: evaluate_model
+ * overrides num_simulations of the baseline AI alone when a baseline is given (:241-246), so the current model keeps
+ * its preset (100 for "easy") while the baseline searches eval_num_sim.  Both must be <= max_simulations. */
+int gz_arena_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration, int32_t opponent,
+                   int32_t sims_b, int64_t games_total, int64_t ordinal_stride, int64_t replay_capacity,
+                   void *stream);
+int gz_arena_get_stats(gz_handle h, gz_arena_stats *out);
 
 /* ---- dataset build ------------------------------------------------------------ */
 /* GomokuSelfPlayDataset + augment_sample (training.py:104-134, 38-70): training samples from packed replay

@@ -252,3 +252,47 @@ def dataset_samples(planes, moves, outcomes, chosen, reference_exact=True):
     if not xs:
         return np.zeros((0, 3, 15, 15), np.float32), np.zeros(0, np.int64), np.zeros(0, np.float32)
     return np.stack(xs), np.asarray(ys, np.int64), np.asarray(vs, np.float32)
+
+
+# ---- evaluation arena: CPU restatement of training.py:221-270 (deterministic mode; test infrastructure) --------------
+def arena_games(orc, games, vs_random, sims_a, sims_b, c_puct, beta, planner_steps, difficulty="easy"):
+    """evaluate_model's loop under the DET patches (random.choice -> seq[0], random.random -> 1.0): game g has side A
+    = black when g is even; A (and B when it is an AlphaZeroGomokuAI) plays the opening book below six stones
+    (ai_agent.py:138-166, first element of the candidate list), otherwise the best move of a search with
+    ai_player = its own colour (the epsilon roll 1.0 never overrides); the RandomAgent plays the first empty cell.
+    sims_a / sims_b: num_simulations of side A / side B.  Returns (list of move lists, winners (0 = none), [W, L, D])."""
+    L = orc.L
+    all_moves, winners, wld = [], [], [0, 0, 0]
+    for g in range(games):
+        side_a = 1 if g % 2 == 0 else 2
+        b = Board()
+        L.gzo_board_init(C.byref(b))
+        moves = []
+        while not b.game_over:
+            empties = [i for i in range(225) if b.cells[i] == 0]
+            if not empties:
+                break
+            mover_is_a = b.to_move == side_a
+            if vs_random and not mover_is_a:
+                mv = empties[0]
+            elif b.move_count < 6:
+                if b.move_count == 0:
+                    mv = 112
+                else:
+                    mv = None
+                    for radius in (1, 2):
+                        ring = [i for i in empties if abs(i // 15 - 7) <= radius and abs(i % 15 - 7) <= radius]
+                        if ring:
+                            mv = ring[0]
+                            break
+                    assert mv is not None
+            else:
+                p = orc.params(sims_a if mover_is_a else sims_b, c_puct, beta, planner_steps, int(b.to_move), difficulty)
+                t = orc.search(b, p)
+                mv = t["stats"].best_move if t["stats"].best_move >= 0 else empties[0]
+            assert L.gzo_make_move(C.byref(b), mv // 15, mv % 15)
+            moves.append(mv)
+        all_moves.append(moves)
+        winners.append(int(b.winner))
+        wld[2 if b.winner == 0 else (0 if b.winner == side_a else 1)] += 1
+    return all_moves, winners, wld

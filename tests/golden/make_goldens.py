@@ -667,9 +667,105 @@ def part_dataset(pool, outdir):
     print("dataset: %d games, %d records, %d samples" % (len(n_all), len(move), sum(len(x) for x in out_moves)))
 
 
+
+# ----------------------------------------------------------------------------- part: arena
+def part_arena(pool, outdir):
+    """training.py:221-270 evaluate_model run as shipped under the DET patches (random.choice -> seq[0],
+    random.random -> 1.0): the RandomAgent then plays the first empty cell in raster order.  Every AlphaZeroGomokuAI
+    the function builds gets time_limit=inf and the shared synthetic planner weights (the reference draws fresh
+    random planner nets per AI, bg_planner.py:210-211); GomokuBoard is wrapped only to log the moves.
+    evaluate_model overrides num_simulations of the opponent only when a baseline is given (:241-246) and side A
+    keeps its preset (100 for "easy"); to keep this affordable the wrapper lowers every new AI's preset to PRESET_SIMS,
+    so with a baseline A searches PRESET_SIMS and B eval_num_sim simulations -- the asymmetry is what is pinned."""
+    PRESET_SIMS = 5
+    import training
+    real_init = ai_agent.AlphaZeroGomokuAI.__init__
+
+    def init(self, *a, **k):
+        k["time_limit"] = float("inf")
+        real_init(self, *a, **k)
+        load_weights(self.bg_planner.graph_net, "graphnet")
+        load_weights(self.bg_planner.opp_dqn, "dqn")
+        self.params["num_simulations"] = PRESET_SIMS
+
+    games = []
+
+    class LoggedBoard(GomokuBoard):
+        def __init__(self, *a, **k):
+            super().__init__(*a, **k)
+            self.log = []
+            games.append(self)
+
+        def make_move(self, r, c):
+            ok = super().make_move(r, c)
+            if ok:
+                self.log.append(r * 15 + c)
+            return ok
+
+    cases = [(3, 0, 4, 0), (4, 1, 2, 0), (3, 0, 2, 1), (4, 2, 2, 1)]   # sims, planner_steps, games, baseline?
+    out = dict(cases=np.array([c + (PRESET_SIMS,) for c in cases], np.int32), moves=[], winner=[], n_moves=[], case_of=[], result=[])
+    ai_agent.AlphaZeroGomokuAI.__init__ = init
+    training.GomokuBoard = LoggedBoard
+    det_patch()
+    try:
+        for ci, (sims, plans, ng, base) in enumerate(cases):
+            del games[:]
+            cur = neural_network.GomokuModel(device="cpu")
+            load_weights(cur.model, "pv")
+            t0 = time.time()
+            res = training.evaluate_model(cur, cur if base else None, torch.device("cpu"), games=ng,
+                                          eval_difficulty="easy", eval_num_sim=sims, eval_plans=plans)
+            print("arena case", ci, res, "%.0f s" % (time.time() - t0), flush=True)
+            out["result"].append([res["wins"], res["losses"], res["draws"]])
+            for g in games:
+                out["moves"].append(g.log); out["n_moves"].append(len(g.log))
+                out["winner"].append(0 if g.winner is None else g.winner); out["case_of"].append(ci)
+    finally:
+        det_unpatch()
+        ai_agent.AlphaZeroGomokuAI.__init__ = real_init
+        training.GomokuBoard = GomokuBoard
+    np.savez_compressed(os.path.join(outdir, "arena.npz"), cases=out["cases"], moves=pad_moves(out["moves"], 225),
+                        n_moves=np.array(out["n_moves"], np.int32), winner=np.array(out["winner"], np.int32),
+                        case_of=np.array(out["case_of"], np.int32), result=np.array(out["result"], np.int32))
+    print("arena: %d games" % len(out["moves"]))
+
+
+# ----------------------------------------------------------------------------- part: update
+def part_update(pool, outdir):
+    """training.py:277-337 train_epoch / validate_epoch run as shipped on the first 640 samples of dataset.npz
+    (train: 512, validation: 128; DataLoader batch 128, shuffle=False), the policy-value net loaded with the shared
+    synthetic weights, Adam(8e-4, wd 1e-5) + clip 0.8 + StepLR(2, 0.85) as training.py:387-388.  Two epochs; saves
+    the losses and every parameter / buffer after the update (float32)."""
+    import contextlib
+    import io
+    import training
+    from torch.utils.data import DataLoader, TensorDataset
+    z = np.load(os.path.join(outdir, "dataset.npz"))
+    x = torch.from_numpy(z["planes"][:640].astype(np.float32))
+    y = torch.from_numpy(z["move"][:640])
+    v = torch.from_numpy(z["value"][:640]).reshape(-1, 1)
+    gm = neural_network.GomokuModel(device="cpu")
+    load_weights(gm.model, "pv")
+    opt = torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=2, gamma=0.85)
+    tr = DataLoader(TensorDataset(x[:512], y[:512], v[:512]), batch_size=128, shuffle=False)
+    va = DataLoader(TensorDataset(x[512:], y[512:], v[512:]), batch_size=128, shuffle=False)
+    tl, vl = [], []
+    with contextlib.redirect_stdout(io.StringIO()):
+        for ep in range(2):
+            tl.append(training.train_epoch(gm, tr, opt, torch.device("cpu"), grad_clip=0.8, epoch_index=ep + 1, num_epochs=2))
+            vl.append(training.validate_epoch(gm, va, torch.device("cpu"), epoch_index=ep + 1, num_epochs=2))
+        sched.step()
+    sd = gm.model.state_dict()
+    out = {"param/" + k: t.numpy() for k, t in sd.items()}
+    np.savez_compressed(os.path.join(outdir, "update.npz"), train_loss=np.array(tl, np.float64),
+                        val_loss=np.array(vl, np.float64), lr=np.array([g["lr"] for g in opt.param_groups]), **out)
+    print("update: train", tl, "val", vl)
+
+
 PARTS = dict(positions=part_positions, boards=part_boards, tiers=part_tiers, rollout=part_rollout,
              mcts=part_mcts, planner=part_planner, nets=part_nets, mctsb=part_mctsb, stoch=part_stoch,
-             dataset=part_dataset)
+             dataset=part_dataset, arena=part_arena, update=part_update)
 
 
 def main():

@@ -1,0 +1,145 @@
+"""SURVEY.md 8f rows 3-4 on the B200: the device-resident evaluation arena (gz_arena_*) against the reference's
+evaluate_model fixtures and the oracle's restatement, move for move in deterministic mode; the policy-value update
+on the GPU against the reference's train_epoch fixtures; one whole training iteration end to end."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _planner_sd(weights):
+    return ({k: torch.as_tensor(v) for k, v in weights["graphnet"].items()},
+            {k: torch.as_tensor(v) for k, v in weights["dqn"].items()})
+
+
+def _model(weights):
+    import neural_network
+    gm = neural_network.GomokuModel(device="cuda")
+    gm.model.load_state_dict({k: torch.as_tensor(t) for k, t in weights["pv"].items()}, strict=False)
+    return gm
+
+
+def _games_from_records(rec):
+    import selfplay
+    games = selfplay.split_games(rec)
+    return {g: [int(p["move"]) for p in plies] for g, plies in games.items()}
+
+
+def test_arena_matches_reference_evaluate_model(weights):
+    """The four evaluate_model runs of tests/golden/arena.npz: every game's move list, the winners and the
+    wins / losses / draws dict, bit for bit (fp32 networks, deterministic mode)."""
+    import training
+    z = golden("arena")
+    gm = _model(weights)
+    for ci, (sims, plans, ng, base, preset) in enumerate(z["cases"]):
+        res, rec = training.evaluate_model(gm, gm if base else None, "cuda", games=int(ng), eval_difficulty="easy",
+                                           eval_num_sim=int(sims), eval_plans=int(plans), deterministic=True,
+                                           seed=1, precision="f32", keep_records=True, preset_sims=int(preset),
+                                           planner_weights=_planner_sd(weights))
+        got = _games_from_records(rec)
+        sel = np.flatnonzero(z["case_of"] == ci)
+        assert sorted(got) == list(range(len(sel)))                     # game_id = ordinal
+        for o, i in enumerate(sel):
+            assert got[o] == list(map(int, z["moves"][i][:z["n_moves"][i]])), "case %d game %d" % (ci, o)
+        w, l, d = (int(v) for v in z["result"][ci])
+        assert res == {"wins": w, "losses": l, "draws": d, "win_rate": w / max(1, w + l + d)}
+
+
+@pytest.mark.parametrize("vs_random,sims_a,sims_b,plans", [(True, 6, 6, 1), (False, 9, 4, 0), (False, 3, 7, 2)])
+def test_arena_matches_oracle_with_recycled_slots(weights, oracle, vs_random, sims_a, sims_b, plans):
+    """10 games in 4 slots (slots are recycled, the last generation is only half counted), asymmetric budgets."""
+    import ai_agent
+    import oracle as orc
+    import training
+    ai = ai_agent.AlphaZeroGomokuAI(1, "easy", device="cuda", planner_steps=plans, deterministic=True, seed=3)
+    ai.params["num_simulations"] = sims_a
+    gs, ds = _planner_sd(weights)
+    ai.bg_planner.graph_net.load_state_dict(gs, strict=False)
+    ai.bg_planner.opp_dqn.load_state_dict(ds, strict=False)
+    ai.model = _model(weights)
+    arena = training.Arena(ai, 10, vs_random=vs_random, sims_b=sims_b, concurrent=4)
+    st, rec = arena.run(keep_records=True)
+    want_moves, want_winner, wld = orc.arena_games(oracle, 10, vs_random, sims_a, sims_b, 1.4, 0.2, plans, "easy")
+    got = _games_from_records(rec)
+    assert sorted(got) == list(range(10))
+    for g in range(10):
+        assert got[g] == want_moves[g], "game %d" % g
+    assert [st["wins"], st["losses"], st["draws"]] == wld and st["games_finished"] == 10
+
+
+def test_stochastic_arena_beats_random_and_counts_add_up():
+    """Real Philox randomness, bf16 networks: 64 games against the RandomAgent.  Every record replays through the
+    host board; A (whose colour alternates with the ordinal) wins nearly always."""
+    import selfplay
+    import training
+    from gomoku_board import GomokuBoard
+    gm = __import__("neural_network").GomokuModel(device="cuda")
+    res, rec = training.evaluate_model(gm, None, "cuda", games=64, eval_num_sim=24, eval_plans=1, seed=5,
+                                       keep_records=True)
+    assert res["wins"] + res["losses"] + res["draws"] == 64
+    games = selfplay.split_games(rec)
+    assert sorted(games) == list(range(64))
+    a_wins = 0
+    for g, plies in games.items():
+        b = GomokuBoard()
+        for p in plies:
+            assert int(p["mover"]) == b.current_player
+            assert b.make_move(int(p["move"]) // 15, int(p["move"]) % 15)
+        assert b.game_over
+        side_a = 1 if g % 2 == 0 else 2
+        a_wins += b.winner == side_a
+        a_plies = [p for p in plies if int(p["mover"]) == side_a]
+        first = a_plies[0]["move"]
+        assert abs(int(first) // 15 - 7) <= 1 and abs(int(first) % 15 - 7) <= 1     # A opens from the book
+    assert a_wins == res["wins"] and res["wins"] >= 48
+
+
+def test_update_on_gpu_matches_reference_train_epoch(weights):
+    """Same batches as the CPU fixture; cuDNN / cuBLAS fp32 against the reference's CPU fp32: losses within 1e-3
+    relative, parameters within 2e-3 absolute after two epochs of Adam."""
+    import training
+    z, d = golden("update"), golden("dataset")
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    x = torch.from_numpy(d["planes"][:640].astype(np.float32)).cuda()
+    y = torch.from_numpy(d["move"][:640]).cuda()
+    v = torch.from_numpy(d["value"][:640]).reshape(-1, 1).cuda()
+    gm = _model(weights)
+    opt = torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5)
+
+    def batches(lo, hi):
+        return [(x[i:i + 128], y[i:i + 128], v[i:i + 128]) for i in range(lo, hi, 128)]
+
+    tl, vl = [], []
+    for ep in range(2):
+        tl.append(training.train_epoch(gm, batches(0, 512), opt, "cuda", grad_clip=0.8))
+        vl.append(training.validate_epoch(gm, batches(512, 640), "cuda"))
+    assert np.allclose(tl, z["train_loss"], rtol=1e-3), (tl, z["train_loss"])
+    assert np.allclose(vl, z["val_loss"], rtol=1e-3), (vl, z["val_loss"])
+    for k, t in gm.model.state_dict().items():
+        if "num_batches_tracked" not in k:
+            assert np.allclose(t.cpu().numpy(), z["param/" + k], rtol=0, atol=2e-3), k
+
+
+def test_one_training_iteration_end_to_end():
+    """Self-play -> dataset (device decode, 35 % x 8 symmetries) -> two epochs -> arena: the loss is finite, the
+    engine picks up the UPDATED weights (predict changes), every phase is timed."""
+    import neural_network
+    import training
+    gm = neural_network.GomokuModel(device="cuda")
+    opt = torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=2, gamma=0.85)
+    cells = np.zeros(225, np.uint8); cells[112] = 1; cells[96] = 2
+    before, _ = gm.predict_batch(cells[None])
+    out = training.run_iteration(gm, opt, sched, "cuda", games_per_iteration=32, concurrent=32, difficulty="easy",
+                                 planner_steps=1, num_simulations=16, eval_games=8, seed=2)
+    assert out["games"] >= 32 and out["records"] > 32 * 9
+    assert out["samples"] == out["records"] + 8 * max(1, int(out["records"] * 0.35))
+    assert np.isfinite(out["train_loss"]) and np.isfinite(out["val_loss"]) and 0 < out["val_loss"] < 20
+    assert sum(out["eval"][k] for k in ("wins", "losses", "draws")) == 8
+    assert set(out["phases"]) == {"selfplay_s", "gather_s", "dataset_s", "update_s", "eval_s"}
+    after, _ = gm.predict_batch(cells[None])
+    assert np.abs(after - before).max() > 1e-6
