@@ -407,6 +407,70 @@ def run_selfplay(args):
         dist.destroy_process_group()
 
 
+def run_iteration(args):
+    """BASELINE config 5: one training.py iteration (training.py:401-508) -- hard-preset self-play on every GPU until
+    --min-games games per rank are finished, NCCL all-gather of the packed replay, device dataset build (35 % x 8
+    symmetries), two epochs of the CE+MSE Adam update (batch 128 x ranks; every rank runs the reference's single
+    trainer on the gathered set), weight broadcast, evaluation arena.  Reports games/h of the WHOLE iteration and the
+    wall time of every phase (max over ranks)."""
+    import torch
+    import neural_network
+    import training
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    torch.manual_seed(1234)
+    gm = neural_network.GomokuModel(device=str(dev))
+    opt = torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=2, gamma=0.85)
+    kw = dict(games_per_iteration=args.min_games * world, concurrent=args.games, difficulty="hard", beta=0.2,
+              planner_steps=5, num_simulations=PRESET["sims"], c_puct=PRESET["c_puct"], batch_size=128 * world,
+              eval_games=args.eval_games, rank=rank, world=world, precision=args.precision)
+    if args.warmup:   # a short untimed iteration: allocations, cuDNN autotune, NCCL rings
+        training.run_iteration(gm, opt, None, dev, seed=1, **dict(kw, games_per_iteration=world, num_simulations=8,
+                                                                  eval_games=0))
+    if dist is not None:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = training.run_iteration(gm, opt, sched, dev, seed=2, **kw)
+    torch.cuda.synchronize()
+    t = time.perf_counter() - t0
+    clocks = sampler.finish()
+    ph = out["phases"]
+    vals = torch.tensor([t, ph["selfplay_s"], ph["gather_s"], ph["dataset_s"], ph["update_s"], ph["eval_s"]],
+                        dtype=torch.float64, device="cuda")
+    games = torch.tensor([float(out["games"])], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        dist.all_reduce(games, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        tt = vals[0].item()
+        print(json.dumps({
+            "metric": "training_iteration_games_per_hour", "value": games.item() / tt * 3600.0, "unit": "games/h",
+            "n_gpus": world, "steps": 1, "warmup": int(bool(args.warmup)), "ms_per_step": tt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
+            "data": "synthetic",
+            "config": config_dict(args.games, world, {"workload": "training.py full iteration (BASELINE config 5): hard "
+                                  "preset self-play (%d games per GPU, %d concurrent) + replay all-gather + dataset "
+                                  "build + 2 epochs CE+MSE Adam + %d evaluation games" %
+                                  (args.min_games, args.games, args.eval_games)}),
+            "clocks": clocks, "games": games.item(), "records": out["records"], "samples": out["samples"],
+            "train_loss": out.get("train_loss"), "val_loss": out.get("val_loss"), "eval": out.get("eval"),
+            "phases_s": {k: round(v, 4) for k, v in zip(("total", "selfplay", "gather", "dataset", "update", "eval"),
+                                                        vals.tolist())}}))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def synthetic_records(n, seed):
     """n packed replay records (72 B) of random mid-game positions, vectorised: stone k of a random permutation
     of the cells goes to colour k & 1, the record's move is the next cell of the permutation."""
@@ -540,15 +604,18 @@ def main():
                     help="independent game groups advanced on separate CUDA streams (0 = engine default)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
                     help="network arithmetic: bf16 tcgen05 (timed mode) or fp32 FFMA (parity mode)")
-    ap.add_argument("--mode", default="search", choices=["search", "selfplay", "dataset"],
+    ap.add_argument("--mode", default="search", choices=["search", "selfplay", "dataset", "iteration"],
                     help="search: sims/s on fixed positions (the headline); selfplay: games/hour; "
                          "dataset: training samples/s of the dataset build (SURVEY 8f row 2)")
     ap.add_argument("--records", type=int, default=1 << 20, help="dataset mode: replay records per GPU")
     ap.add_argument("--min-games", type=int, default=4096, help="selfplay mode: games to finish per rank")
     ap.add_argument("--max-plies", type=int, default=2000)
+    ap.add_argument("--eval-games", type=int, default=64, help="iteration mode: evaluation arena games")
     args = ap.parse_args()
     if args.mode == "selfplay" and args.impl != "reference":
         return run_selfplay(args)
+    if args.mode == "iteration" and args.impl != "reference":
+        return run_iteration(args)
     if args.mode == "dataset" and args.impl != "reference":
         return run_dataset(args)
     if args.impl == "reference":
