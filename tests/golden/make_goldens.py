@@ -703,6 +703,8 @@ def part_arena(pool, outdir):
             return ok
 
     cases = [(3, 0, 4, 0), (4, 1, 2, 0), (3, 0, 2, 1), (4, 2, 2, 1)]   # sims, planner_steps, games, baseline?
+    if os.environ.get("GZ_ARENA_CASES"):   # subset (the engine-vs-engine cases cost the reference ~25-60 minutes each)
+        cases = [cases[int(i)] for i in os.environ["GZ_ARENA_CASES"].split(",")]
     out = dict(cases=np.array([c + (PRESET_SIMS,) for c in cases], np.int32), moves=[], winner=[], n_moves=[], case_of=[], result=[])
     ai_agent.AlphaZeroGomokuAI.__init__ = init
     training.GomokuBoard = LoggedBoard
@@ -735,7 +737,7 @@ def part_update(pool, outdir):
     """training.py:277-337 train_epoch / validate_epoch run as shipped on the first 640 samples of dataset.npz
     (train: 512, validation: 128; DataLoader batch 128, shuffle=False), the policy-value net loaded with the shared
     synthetic weights, Adam(8e-4, wd 1e-5) + clip 0.8 + StepLR(2, 0.85) as training.py:387-388.  Two epochs; saves
-    the losses and every parameter / buffer after the update (float32)."""
+    the losses and every parameter / buffer after the update (float32; large tensors subsampled)."""
     import contextlib
     import io
     import training
@@ -757,7 +759,8 @@ def part_update(pool, outdir):
             vl.append(training.validate_epoch(gm, va, torch.device("cpu"), epoch_index=ep + 1, num_epochs=2))
         sched.step()
     sd = gm.model.state_dict()
-    out = {"param/" + k: t.numpy() for k, t in sd.items()}
+    # tensors above 4096 elements are stored as every 37th element of the flattened tensor (fixture size)
+    out = {"param/" + k: (t.numpy() if t.numel() <= 4096 else t.numpy().reshape(-1)[::37]) for k, t in sd.items()}
     np.savez_compressed(os.path.join(outdir, "update.npz"), train_loss=np.array(tl, np.float64),
                         val_loss=np.array(vl, np.float64), lr=np.array([g["lr"] for g in opt.param_groups]), **out)
     print("update: train", tl, "val", vl)

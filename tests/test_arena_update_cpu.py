@@ -10,6 +10,11 @@ import torch
 from conftest import golden
 
 
+def _sub(a):
+    """update.npz stores tensors above 4096 elements as every 37th element of the flattened tensor."""
+    return a if a.size <= 4096 else a.reshape(-1)[::37]
+
+
 def _golden_games(z, case):
     sel = np.flatnonzero(z["case_of"] == case)
     return [list(map(int, z["moves"][i][:z["n_moves"][i]])) for i in sel], [int(z["winner"][i]) for i in sel]
@@ -73,7 +78,7 @@ def test_update_matches_reference_train_epoch(weights):
     sd = gm.model.state_dict()
     assert len([k for k in z.files if k.startswith("param/")]) == len(sd) == 45
     for k, t in sd.items():
-        assert np.allclose(t.numpy(), z["param/" + k], rtol=0, atol=1e-6), k
+        assert np.allclose(_sub(t.numpy()), z["param/" + k], rtol=0, atol=1e-6), k
 
 
 def test_simple_replay_from_records_matches_reference_lists():

@@ -10,6 +10,11 @@ from conftest import golden
 pytestmark = pytest.mark.gpu
 
 
+def _sub(a):
+    """update.npz stores tensors above 4096 elements as every 37th element of the flattened tensor."""
+    return a if a.size <= 4096 else a.reshape(-1)[::37]
+
+
 def _planner_sd(weights):
     return ({k: torch.as_tensor(v) for k, v in weights["graphnet"].items()},
             {k: torch.as_tensor(v) for k, v in weights["dqn"].items()})
@@ -123,7 +128,7 @@ def test_update_on_gpu_matches_reference_train_epoch(weights):
     assert np.allclose(vl, z["val_loss"], rtol=1e-3), (vl, z["val_loss"])
     for k, t in gm.model.state_dict().items():
         if "num_batches_tracked" not in k:
-            assert np.allclose(t.cpu().numpy(), z["param/" + k], rtol=0, atol=2e-3), k
+            assert np.allclose(_sub(t.cpu().numpy()), z["param/" + k], rtol=0, atol=2e-3), k
 
 
 def test_one_training_iteration_end_to_end():
