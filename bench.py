@@ -42,6 +42,26 @@ STAGE_BYTES = {"tree": ("simulations", 80 + 100 + 48), "planner_score": ("planne
 PRESET = dict(sims=200, c_puct=1.8, beta=0.2, planner_steps=5, difficulty="hard")
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on
+    fd 1 under torchrun), so fd 1 is pointed at stderr for the whole run and the JSON line goes to a private
+    duplicate of the original stdout."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -176,7 +196,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": "sims/s", "cores": threads, "kind": "port",
                              "sample": sample},
             "e2e": {"value": value, "unit": "sims/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(json.dumps(line))
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's main kernel, from the committed
@@ -320,7 +340,7 @@ def run_engine(args):
                 "flops_per_sim": f_sim,
                 "tensor_frac_whole_step": value * f_sim / 1e12 / peaks["tf_sustained"] / world,
                 "counters": cnt}
-        print(json.dumps(line))
+        emit(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
 
@@ -391,7 +411,7 @@ def run_selfplay(args):
     if rank == 0:
         t = mx[0].item() / 1e3
         games, plies, sims = vals[1].item(), vals[2].item(), vals[3].item()
-        print(json.dumps({
+        emit(json.dumps({
             "metric": "selfplay_games_per_hour", "value": games / t * 3600.0, "unit": "games/h", "n_gpus": world,
             "steps": steps, "warmup": args.warmup, "ms_per_step": mx[0].item() / steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
@@ -454,7 +474,7 @@ def run_iteration(args):
         dist.all_reduce(games, op=dist.ReduceOp.SUM)
     if rank == 0:
         tt = vals[0].item()
-        print(json.dumps({
+        emit(json.dumps({
             "metric": "training_iteration_games_per_hour", "value": games.item() / tt * 3600.0, "unit": "games/h",
             "n_gpus": world, "steps": 1, "warmup": int(bool(args.warmup)), "ms_per_step": tt * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
@@ -570,7 +590,7 @@ def run_dataset(args):
         per_sample = 675 * 4 + 8 + 4            # written
         bytes_step = count * per_sample + n * 72 + len(chosen) * 4
         gbs = bytes_step * args.steps / (t[0].item() / 1e3) / 1e9
-        print(json.dumps({
+        emit(json.dumps({
             "metric": "dataset_samples_per_sec", "value": world * count * args.steps / (t[0].item() / 1e3),
             "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": t[0].item() / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -612,6 +632,7 @@ def main():
     ap.add_argument("--max-plies", type=int, default=2000)
     ap.add_argument("--eval-games", type=int, default=64, help="iteration mode: evaluation arena games")
     args = ap.parse_args()
+    claim_stdout()
     if args.mode == "selfplay" and args.impl != "reference":
         return run_selfplay(args)
     if args.mode == "iteration" and args.impl != "reference":
