@@ -261,6 +261,7 @@ void nn_heads_bf16(Engine &e, bool pv, const gz_board *boards, const uint8_t *ac
                    float *logits, float *probs, float *value, float *prior, const int32_t *prior_slot,
                    cudaStream_t s);
 void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStream_t s);
+void nn_gnhead_dqn_bf16(Engine &e, const gz_board *boards, int G, float *policy, float *dqn_q, cudaStream_t s);
 // precision dispatch
 void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
                    float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s);

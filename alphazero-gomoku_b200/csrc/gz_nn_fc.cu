@@ -85,9 +85,10 @@ __device__ __forceinline__ void store_rows_scalar_affine(float *stage, int lane,
     }
 }
 
-__global__ void __launch_bounds__(192, 1)
-k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict__ w_packed,
-           const float *__restrict__ bias /*[3][256]*/, float *__restrict__ q) {
+// body of k_dqn_umma for one tile of 128 boards (also one half of k_gnhead_dqn)
+__device__ __forceinline__ void dqn_body(const int tile, const gz_board *__restrict__ boards, int G,
+                                         const uint8_t *__restrict__ w_packed,
+                                         const float *__restrict__ bias /*[3][256]*/, float *__restrict__ q) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *abuf = smem;                                        // [2][kChunkBytesA]
     uint8_t *a2 = abuf + 2 * kChunkBytesA;                       // [32 k-groups][128][8]
@@ -100,7 +101,6 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 14);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x;
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&a_full[i], 128); ptx::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < kWStages; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
@@ -265,7 +265,7 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
         }
 #ifdef GZ_HEAD_TIMING
         tq[6] = clock64();
-        if (blockIdx.x == 0 && threadIdx.x == 64)
+        if (tile == 0 && threadIdx.x == 64)
             printf("dqn: vector %lld, L1 operands %lld, wait L1 %lld, epi1+wait L2 %lld, epi2+wait L3 %lld, epi3 %lld cycles\n",
                    tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4], tq[6] - tq[5]);
 #endif
@@ -273,6 +273,12 @@ k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+__global__ void __launch_bounds__(192, 1)
+k_dqn_umma(const gz_board *__restrict__ boards, int G, const uint8_t *__restrict__ w_packed,
+           const float *__restrict__ bias, float *__restrict__ q) {
+    dqn_body(blockIdx.x, boards, G, w_packed, bias, q);
 }
 
 void nn_dqn_bf16(Engine &e, const gz_board *boards, int G, float *dqn_q, cudaStream_t s) {
@@ -324,7 +330,7 @@ struct HeadArgs {
 };
 
 template <bool PV>
-__global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
+__device__ __forceinline__ void head_body(const int tile, const HeadArgs &a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *abuf = smem;                                   // [2 buffers][hi, lo][kChunkBytesA]
     uint8_t *wbuf = abuf + 4 * kChunkBytesA;                // [kWStages][kHdWBytesP]
@@ -337,7 +343,6 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
     constexpr int kChunks = kHdChunksP + (PV ? kHdChunksV : 0);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x;
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < kWStages; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
@@ -514,7 +519,7 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
         }
 #ifdef GZ_HEAD_TIMING
         tt[6] = clock64();
-        if (blockIdx.x == 0 && threadIdx.x == 64)
+        if (tile == 0 && threadIdx.x == 64)
             printf("head PV=%d: operands %lld, wait mma %lld, softmax pass1 %lld, pass2+stores %lld, prior %lld, value %lld cycles\n",
                    (int)PV, tt[1] - tt[0], tt[2] - tt[1], tt[3] - tt[2], tt[4] - tt[3], tt[5] - tt[4], tt[6] - tt[5]);
 #endif
@@ -522,6 +527,21 @@ __global__ void __launch_bounds__(192, 1) k_head_umma(HeadArgs a) {
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+template <bool PV>
+__global__ void __launch_bounds__(192, 1) k_head_umma(const __grid_constant__ HeadArgs a) {
+    head_body<PV>(blockIdx.x, a);
+}
+
+// GraphNet head and OpponentDQN of one planner step in ONE launch: both are latency-bound chains on 32 CTAs
+// (4096 boards / 128), independent of each other, and k_planner_pick needs both.  CTAs [0, head_tiles) run the head,
+// the rest the DQN, so the two chains overlap on different SMs: ~23 us instead of 2 x 23 us per planner step.
+__global__ void __launch_bounds__(192, 1)
+k_gnhead_dqn(const __grid_constant__ HeadArgs a, int head_tiles, const uint8_t *__restrict__ dqn_w,
+             const float *__restrict__ dqn_bias, float *__restrict__ dqn_q) {
+    if ((int)blockIdx.x < head_tiles) head_body<false>(blockIdx.x, a);
+    else dqn_body((int)blockIdx.x - head_tiles, a.boards, a.G, dqn_w, dqn_bias, dqn_q);
 }
 
 void nn_heads_bf16(Engine &e, bool pv, const gz_board *boards, const uint8_t *active, int G, float *policy,
@@ -543,6 +563,24 @@ void nn_heads_bf16(Engine &e, bool pv, const gz_board *boards, const uint8_t *ac
     prof_begin(e, pv ? GZ_STAGE_PV_HEADS : GZ_STAGE_GN_HEAD, 1, s);
     if (pv) k_head_umma<true><<<(G + 127) / 128, 192, kSmemHead, s>>>(a);
     else k_head_umma<false><<<(G + 127) / 128, 192, kSmemHead, s>>>(a);
+    prof_end(e, s);
+}
+
+// GraphNet head (softmax into `policy`, pitch kPolicyPitch) + OpponentDQN, one launch (k_gnhead_dqn)
+void nn_gnhead_dqn_bf16(Engine &e, const gz_board *boards, int G, float *policy, float *dqn_q, cudaStream_t s) {
+    static bool configured = false;
+    constexpr int kSmemBoth = kSmemHead > kSmemDqn ? kSmemHead : kSmemDqn;
+    if (!configured) {
+        cudaFuncSetAttribute(k_gnhead_dqn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBoth);
+        configured = true;
+    }
+    HeadArgs a = {};
+    a.pc = e.gn_pc; a.boards = boards; a.w_pol = e.bw.gn_hfc_w; a.b_pol = e.bw.gn_hfc_b;
+    a.vfc1_b = e.pv.vfc1_b; a.vfc2_w = e.pv.vfc2_w; a.vfc2_b = e.pv.vfc2_b;
+    a.policy = policy; a.prior_cap = e.tree.cap; a.G = G;
+    const int tiles = (G + 127) / 128;
+    prof_begin(e, GZ_STAGE_GN_HEAD, 1, s);
+    k_gnhead_dqn<<<2 * tiles, 192, kSmemBoth, s>>>(a, tiles, e.bw.dqn_w, e.bw.dqn_bias, dqn_q);
     prof_end(e, s);
 }
 

@@ -365,9 +365,12 @@ void nn_planner_forward(Engine &e, const gz_board *boards, int G, float *gn_logi
         nn_graphnet_convs_bf16(e, boards, nullptr, G, s);      // ends with the fused head conv -> e.gn_pc
         const bool internal = policy_pitch == kPolicyPitch;
         // the search and the planner only read the softmax (pitch kPolicyPitch); logits are an API output
-        nn_heads_bf16(e, false, boards, nullptr, G, internal ? gn_policy : nullptr, internal ? nullptr : gn_logits,
-                      internal ? nullptr : gn_policy, nullptr, nullptr, nullptr, s);
-        nn_dqn_bf16(e, boards, G, dqn_q, s);
+        if (internal) {
+            nn_gnhead_dqn_bf16(e, boards, G, gn_policy, dqn_q, s);   // head + DQN in one launch
+        } else {
+            nn_heads_bf16(e, false, boards, nullptr, G, nullptr, gn_logits, gn_policy, nullptr, nullptr, nullptr, s);
+            nn_dqn_bf16(e, boards, G, dqn_q, s);
+        }
     } else {
         nn_planner_forward_fp32(e, boards, G, gn_logits, gn_policy, policy_pitch, dqn_q, s);
     }

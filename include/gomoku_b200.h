@@ -301,8 +301,8 @@ enum {
     GZ_STAGE_PV_HEADS = 3,     /* policy / value heads, softmax, prior */
     GZ_STAGE_PLAN_SCORE = 4,   /* knowledge-search scoring + top-k */
     GZ_STAGE_GN_CONVS = 5,     /* GraphNet convolutions */
-    GZ_STAGE_GN_HEAD = 6,      /* GraphNet head + softmax */
-    GZ_STAGE_DQN = 7,          /* OpponentDQN */
+    GZ_STAGE_GN_HEAD = 6,      /* GraphNet head + softmax; inside gz_search (bf16) also OpponentDQN: one launch */
+    GZ_STAGE_DQN = 7,          /* OpponentDQN when launched alone (gz_planner_nets_forward, fp32 mode) */
     GZ_STAGE_PLAN_PICK = 8,    /* blend, explore roll, make_move */
     GZ_STAGE_ROLLOUT = 9,      /* offensive-random tail */
     GZ_STAGE_MISC = 10,        /* import / export / finalize */

@@ -758,11 +758,15 @@ def part_update(pool, outdir):
             tl.append(training.train_epoch(gm, tr, opt, torch.device("cpu"), grad_clip=0.8, epoch_index=ep + 1, num_epochs=2))
             vl.append(training.validate_epoch(gm, va, torch.device("cpu"), epoch_index=ep + 1, num_epochs=2))
         sched.step()
+    gm.eval_mode()
+    with torch.no_grad():      # the updated network as a function: outputs on the validation samples
+        val_logits, val_value = gm.model(x[512:])
     sd = gm.model.state_dict()
     # tensors above 4096 elements are stored as every 37th element of the flattened tensor (fixture size)
     out = {"param/" + k: (t.numpy() if t.numel() <= 4096 else t.numpy().reshape(-1)[::37]) for k, t in sd.items()}
     np.savez_compressed(os.path.join(outdir, "update.npz"), train_loss=np.array(tl, np.float64),
-                        val_loss=np.array(vl, np.float64), lr=np.array([g["lr"] for g in opt.param_groups]), **out)
+                        val_loss=np.array(vl, np.float64), val_logits=val_logits.numpy(),
+                        val_value=val_value.numpy().reshape(-1), lr=np.array([g["lr"] for g in opt.param_groups]), **out)
     print("update: train", tl, "val", vl)
 
 

@@ -75,6 +75,11 @@ def test_update_matches_reference_train_epoch(weights):
     assert np.allclose(tl, z["train_loss"], rtol=0, atol=1e-6), (tl, z["train_loss"])
     assert np.allclose(vl, z["val_loss"], rtol=0, atol=1e-6), (vl, z["val_loss"])
     assert np.allclose([g["lr"] for g in opt.param_groups], z["lr"])
+    gm.eval_mode()
+    with torch.no_grad():
+        lg, val = gm.model(x[512:])
+    assert np.allclose(lg.numpy(), z["val_logits"], rtol=0, atol=1e-5)
+    assert np.allclose(val.numpy().reshape(-1), z["val_value"], rtol=0, atol=1e-5)
     sd = gm.model.state_dict()
     assert len([k for k in z.files if k.startswith("param/")]) == len(sd) == 45
     for k, t in sd.items():
