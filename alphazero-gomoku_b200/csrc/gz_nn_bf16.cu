@@ -381,7 +381,7 @@ struct GnBlockCfg {
     static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
     static constexpr int MID_BYTES = 8 * 256 * 16;
     static constexpr int W3_BYTES = 9 * 8 * 64 * 16, W1_BYTES = 8 * 64 * 16;
-    static constexpr int SMEM = 2 * SLAB_BYTES + 2 * MID_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
+    static constexpr int SMEM = 2 * SLAB_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
 };
 
 // Biases (and the head's 1x1 weights) travel as a kernel parameter: after unrolling every index is a
@@ -405,8 +405,7 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     using C = GnBlockCfg;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *slab = smem;
-    uint8_t *mid = slab + 2 * C::SLAB_BYTES;
-    uint8_t *sw3 = mid + 2 * C::MID_BYTES;
+    uint8_t *sw3 = slab + 2 * C::SLAB_BYTES;
     uint8_t *sw1 = sw3 + C::W3_BYTES;
     float *sb3 = reinterpret_cast<float *>(sw1 + C::W1_BYTES);
     float *sb1 = sb3 + 64;
@@ -454,7 +453,7 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     } else if (warp == 1) {
         {   // whole warp; one elected lane issues (gz_tcgen05.cuh)
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 64);
-            constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_M = 256 * 16, LBO_B = 64 * 16;
+            constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = 64 * 16;
             ptx::mbar_wait(w_full, 0);
             const uint32_t w3_addr = ptx::smem_u32(sw3), w1_addr = ptx::smem_u32(sw1);
             for (int it = 0; it <= n_it; ++it) {
@@ -491,15 +490,16 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     ptx::mbar_wait(&mid_full[jb], par);
                     ptx::mbar_wait(&d2_empty[jb], par ^ 1);
                     ptx::tc_fence_after();
-                    const uint64_t dm0 = ptx::make_desc(ptx::smem_u32(mid + jb * C::MID_BYTES), LBO_M, 128);
+                    // A = the 3x3 result packed to bf16 in place in its accumulator columns (epilogue 1): TS form
                     const uint64_t dw0 = ptx::make_desc(w1_addr, LBO_B, 128);
                     const uint32_t acc = tmem_base + 256 + jb * 128;
+                    const uint32_t amid = tmem_base + jb * 128;
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            ptx::umma_bf16_elect(acc + h * 64, dm0 + (uint64_t)(2 * k * 256 + 128 * h),
-                                                 dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
+                            ptx::umma_bf16_ts_elect(acc + h * 64, amid + h * 64 + 8 * k,
+                                                    dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
                     ptx::umma_commit_elect(&mid_empty[jb]);
                     ptx::umma_commit_elect(&d2_full[jb]);
                 }
@@ -518,7 +518,8 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                 ptx::mbar_wait(&d1_full[ab], par);
                 ptx::mbar_wait(&mid_empty[ab], par ^ 1);
                 ptx::tc_fence_after();
-                uint8_t *dst = mid + ab * C::MID_BYTES + row * 16;
+                // bias + ReLU + bf16 pack, written back IN PLACE over the accumulator's first 32 columns (the write
+                // cursor c0/2 never passes the read cursor c0): the 1x1 reads it as its A operand from TMEM
 #pragma unroll
                 for (int c0 = 0; c0 < 64; c0 += 16) {
                     float v[16];
@@ -528,11 +529,10 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     for (int i = 0; i < 8; ++i)
                         pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + kc.b3[c0 + 2 * i], 0.f),
                                                fmaxf(v[2 * i + 1] + kc.b3[c0 + 2 * i + 1], 0.f));
-                    *reinterpret_cast<uint4 *>(dst + (c0 / 8) * 4096) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4 *>(dst + (c0 / 8 + 1) * 4096) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    ptx::tmem_st8(tlane + ab * 128 + c0 / 2, pk);
                 }
+                ptx::tmem_wait_st();
                 ptx::tc_fence_before();
-                ptx::fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
             }
