@@ -375,7 +375,7 @@ k_planes_to_nchw(const uint8_t *__restrict__ planes, int C, const uint8_t *__res
 // Both weight sets are resident in shared memory; slabs, mid tiles and both accumulators are double
 // buffered, and the issuer runs one board ahead with the 3x3 so the tensor pipe never waits for an
 // epilogue:  MMA3(0) MMA3(1) MMA1(0) MMA3(2) MMA1(1) ...
-//   warp 0     slab producer (bulk copies)          warp 1     tcgen05.mma issuer
+//   warp 0     slab producer (bulk copies)          warps 1, 10  tcgen05.mma issuers (M half 0 / 1)
 //   warps 2-9  epilogues: quadrant = warp & 3, M half = (warp - 2) >> 2
 struct GnBlockCfg {
     static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
@@ -398,7 +398,7 @@ struct GnBlockConsts {
 // bf16 hi/lo operand tiles of the head GEMM, K index channel-major like the flatten at bg_planner.py:55); the 64-channel planes of the
 // last layer are never stored.
 template <bool FINAL>
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__(352, 1)
 k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
            const __grid_constant__ GnBlockConsts kc, uint8_t *__restrict__ out_planes,
            uint8_t *__restrict__ head_out, int G) {
@@ -419,11 +419,11 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     if (FINAL) {
     }
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&a_full[i], 1);   ptx::mbar_init(&a_empty[i], 1);
-            ptx::mbar_init(&d1_full[i], 1);  ptx::mbar_init(&d1_empty[i], 8);
-            ptx::mbar_init(&mid_full[i], 8); ptx::mbar_init(&mid_empty[i], 1);
-            ptx::mbar_init(&d2_full[i], 1);  ptx::mbar_init(&d2_empty[i], 8);
+        for (int i = 0; i < 2; ++i) {   // every tcgen05.commit comes twice: one per issuer warp (M half)
+            ptx::mbar_init(&a_full[i], 1);   ptx::mbar_init(&a_empty[i], 2);
+            ptx::mbar_init(&d1_full[i], 2);  ptx::mbar_init(&d1_empty[i], 8);
+            ptx::mbar_init(&mid_full[i], 8); ptx::mbar_init(&mid_empty[i], 2);
+            ptx::mbar_init(&d2_full[i], 2);  ptx::mbar_init(&d2_empty[i], 8);
         }
         ptx::mbar_init(w_full, 1);
         ptx::fence_mbar_init();
@@ -450,7 +450,10 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                                   src + (size_t)cg * kPlaneBytes, C::SLAB_ROWS * 16, &a_full[ab]);
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == 10) {
+        // Two issuer warps, one per M half of the board (rows 0-127 / 128-255, separate accumulators): while one
+        // sits in its per-board barrier work (commits, waits, fences) the other keeps the tensor pipe fed.
+        const int h = warp == 1 ? 0 : 1;
         {   // whole warp; one elected lane issues (gz_tcgen05.cuh)
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 64);
             constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = 64 * 16;
@@ -469,17 +472,16 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
                     const uint64_t db0 = ptx::make_desc(w3_addr, LBO_B, 128);
                     const uint32_t acc = tmem_base + ab * 128;
+                    const uint32_t acc_h = acc + h * 64;
+                    const uint64_t da_h = da0 + (uint64_t)(128 * h);
 #pragma unroll
                     for (int tap = 0; tap < 9; ++tap) {
                         const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
 #pragma unroll
-                        for (int h = 0; h < 2; ++h)
-#pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                ptx::umma_bf16_elect(acc + h * 64,
-                                                     da0 + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff + 128 * h),
-                                                     db0 + (uint64_t)((tap * 8192 + 2 * k * (int)LBO_B) >> 4),
-                                                     idesc, (tap | k) != 0);
+                        for (int k = 0; k < 4; ++k)
+                            ptx::umma_bf16_elect(acc_h, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff),
+                                                 db0 + (uint64_t)((tap * 8192 + 2 * k * (int)LBO_B) >> 4),
+                                                 idesc, (tap | k) != 0);
                     }
                     ptx::umma_commit_elect(&a_empty[ab]);
                     ptx::umma_commit_elect(&d1_full[ab]);
@@ -495,11 +497,9 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     const uint32_t acc = tmem_base + 256 + jb * 128;
                     const uint32_t amid = tmem_base + jb * 128;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            ptx::umma_bf16_ts_elect(acc + h * 64, amid + h * 64 + 8 * k,
-                                                    dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
+                    for (int k = 0; k < 4; ++k)
+                        ptx::umma_bf16_ts_elect(acc + h * 64, amid + h * 64 + 8 * k,
+                                                dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
                     ptx::umma_commit_elect(&mid_empty[jb]);
                     ptx::umma_commit_elect(&d2_full[jb]);
                 }
@@ -597,8 +597,8 @@ static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, con
     memcpy(kc.b3, e.bw.gn_host_bias[block], sizeof(float) * 128);   // b3 then b1
     memcpy(kc.head_w, e.bw.gn_host_head, sizeof(float) * 130);       // head_w then head_b
     int grid = G < e.sm_count ? G : e.sm_count;
-    if (head_out) k_gn_block<true><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
-    else k_gn_block<false><<<grid, 320, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
+    if (head_out) k_gn_block<true><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
+    else k_gn_block<false><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
 }
 
 // ---- host side -------------------------------------------------------------------------------------
