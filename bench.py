@@ -447,7 +447,7 @@ def run_iteration(args):
     dev = torch.device("cuda", local)
     torch.manual_seed(1234)
     gm = neural_network.GomokuModel(device=str(dev))
-    opt = torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5)
+    opt = torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5, capturable=not args.eager_update)
     sched = torch.optim.lr_scheduler.StepLR(opt, step_size=2, gamma=0.85)
     kw = dict(games_per_iteration=args.min_games * world, concurrent=args.games, difficulty="hard", beta=0.2,
               planner_steps=5, num_simulations=PRESET["sims"], c_puct=PRESET["c_puct"], batch_size=128 * world,
@@ -631,6 +631,8 @@ def main():
     ap.add_argument("--min-games", type=int, default=4096, help="selfplay mode: games to finish per rank")
     ap.add_argument("--max-plies", type=int, default=2000)
     ap.add_argument("--eval-games", type=int, default=64, help="iteration mode: evaluation arena games")
+    ap.add_argument("--eager-update", action="store_true",
+                    help="iteration mode: run the update eagerly instead of replaying one captured CUDA graph per batch")
     args = ap.parse_args()
     claim_stdout()
     if args.mode == "selfplay" and args.impl != "reference":
