@@ -233,7 +233,7 @@ class Engine:
     # ---- planner / rollout
     def _ai(self, ai_player, G):
         a = np.broadcast_to(np.asarray(ai_player, np.uint8), (G,))
-        return self.torch.as_tensor(np.ascontiguousarray(a)).to(self.device)
+        return self.torch.as_tensor(np.array(a, copy=True, order="C")).to(self.device)   # copy: fixtures are read-only
 
     def planner_move(self, boards, ai_player, params, sim=0, step=0):
         t = self.torch
