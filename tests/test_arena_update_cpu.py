@@ -102,3 +102,44 @@ def test_simple_replay_from_records_matches_reference_lists():
     assert hand.outcomes == [1 if p == 1 else -1 for p in rep.players]
     hand2 = training.SimpleReplay(); hand2.add(rep.states[0], 0, 2); hand2.finalize_with_winner(None)
     assert hand2.outcomes == [0]
+
+
+def test_device_loader_feeds_the_same_batches(weights):
+    """DeviceLoader over materialized tensors (here on the CPU: the eager path of train_epoch) yields the batches a
+    DataLoader(Subset(dataset, indices), 128, shuffle=False) would, ragged tail included, and a seeded shuffle is a
+    permutation of the indices."""
+    import random
+    import neural_network
+    import training
+    d = golden("dataset")
+    torch.set_num_threads(1)
+
+    class Data:
+        planes = torch.from_numpy(d["planes"][:300].astype(np.float32))
+        move = torch.from_numpy(d["move"][:300])
+        value = torch.from_numpy(d["value"][:300])
+
+    holder = training._Materialized(Data)
+    idx = list(range(299, -1, -1))
+    got = list(training.DeviceLoader(holder, idx, 128, shuffle=False))
+    assert [b[0].shape[0] for b in got] == [128, 128, 44] and len(training.DeviceLoader(holder, idx, 128)) == 3
+    for k, (x, y, v) in enumerate(got):
+        sel = torch.as_tensor(idx[128 * k:128 * (k + 1)])
+        assert torch.equal(x, Data.planes[sel]) and torch.equal(y, Data.move[sel])
+        assert torch.equal(v, Data.value[sel].reshape(-1, 1))
+    sh = training.DeviceLoader(holder, idx, 128, shuffle=True, rng=random.Random(3))
+    seen = torch.cat([y for _, y, _ in sh])
+    assert sorted(seen.tolist()) == sorted(Data.move.tolist())
+
+    def model():
+        gm = neural_network.GomokuModel(device="cpu")
+        if gm.device.type != "cpu":
+            gm.model.cpu(); gm.device = torch.device("cpu")
+        gm.model.load_state_dict({k: torch.as_tensor(t) for k, t in weights["pv"].items()}, strict=False)
+        return gm, torch.optim.Adam(gm.model.parameters(), lr=8e-4, weight_decay=1e-5)
+
+    ga, oa = model()
+    gb, ob = model()
+    la = training.train_epoch(ga, training.DeviceLoader(holder, idx, 128), oa, torch.device("cpu"), grad_clip=0.8)
+    lb = training.train_epoch(gb, got, ob, torch.device("cpu"), grad_clip=0.8)
+    assert la == lb
