@@ -9,8 +9,9 @@ evaluation / planner-guided playout / backup -- as one `gz_search_host` call on 
 Reference behaviours kept on purpose: UCB1-style score with beta * BG bonus, no
 negamax, one node per simulation in reverse raster order, `params` re-read at every call, `beta` /
 `planner_steps` taken from the constructor (not from `params["bg_weight"]` / `["planning_steps"]`),
-`model` assignable.  The wall-clock `time_limit` is honoured between searches only: a finite limit
-cannot cut a GPU search short, and parity runs use `float("inf")` anyway.
+`model` assignable.  The wall-clock `time_limit` is handed to the engine (gz_search_params.time_limit_s): like
+the reference the search stops starting new simulations once the limit has passed (checked every four waves);
+parity runs use `float("inf")`.
 """
 import logging
 import random
@@ -37,7 +38,7 @@ class AlphaZeroGomokuAI:
 
     def __init__(self, player, difficulty="medium", model_path=None, device=None, beta=0.2,
                  planner_steps=5, time_limit=5.0, time_reward_factor=0.1, deterministic=False,
-                 seed=None, precision="f32"):
+                 seed=None, precision="f32", store_priors=False):
         self.player = player
         self.difficulty = difficulty
         self.name = "AlphaZero_%s" % difficulty
@@ -63,6 +64,8 @@ class AlphaZeroGomokuAI:
         # precision of the networks inside the engine: "f32" (FFMA, 1e-4 against torch) or "bf16"
         # (tcgen05 tensor cores, 2e-2): the throughput mode for batched self-play
         self.precision = precision
+        # keep MCTSNode.prior_prob per node (ai_agent.py:522-523 there: computed, never read by the search)
+        self.store_priors = bool(store_priors)
         self.deterministic = bool(deterministic)
         self.seed = random.getrandbits(63) if seed is None else int(seed)
         self._engine = None
@@ -78,7 +81,8 @@ class AlphaZeroGomokuAI:
             cap_g = max(n_games, 1)
             e = _engine.Engine(max_games=cap_g, max_simulations=max(sims, 8),
                                device=self.device.index or 0,
-                               precision=1 if self.precision == "bf16" else 0)
+                               precision=1 if self.precision == "bf16" else 0,
+                               store_priors=self.store_priors)
             self._engine, self._packed = e, (None, None)
             self.knowledge_search._engine = e
         pv_v = weights_version(self.model.model)
@@ -100,7 +104,7 @@ class AlphaZeroGomokuAI:
                                 _engine.PLANNER_PRESETS else "medium",
                                 deterministic=self.deterministic,
                                 seed=(self.seed + 0x9E3779B97F4A7C15 * self._searches) & (2 ** 64 - 1),
-                                game_base=game_base)
+                                game_base=game_base, time_limit=self.time_limit)
         bp = self.bg_planner.params
         p.planner_k, p.planner_alpha, p.planner_explore = bp["k"], bp["mix_alpha"], bp["explore"]
         return p
@@ -161,6 +165,12 @@ class AlphaZeroGomokuAI:
         self._searches += 1
         cv, cval, best = eng.search_host(cells, to_move, count, ai, p)
         return {"child_visits": cv, "child_value": cval, "best_move": best}
+
+    def root_prior_prob(self, board, index=0):
+        """MCTSNode.prior_prob of the root of the last search (ai_agent.py:564-582 there): the network's softmax
+        gathered over `board`'s valid moves in raster order and renormalised.  Needs store_priors=True."""
+        pr, _ = self._engine.get_priors(index, 0)
+        return np.array([pr[r * board.BOARD_SIZE + c] for r, c in board.get_valid_moves()], np.float64)
 
     def get_moves(self, boards):
         """Batched get_move (book, search, epsilon override) for many independent boards."""

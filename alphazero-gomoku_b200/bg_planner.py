@@ -145,21 +145,30 @@ class BGPlannerAI:
         return self._engine
 
     def get_move(self, board):
+        """bg_planner.py:232-269.  Knowledge-search top-k, network blend and argmax run in the engine (one
+        gz_planner_move call, deterministic pick); the explore roll stays on the host with Python's `random`
+        exactly where the reference has it -- one random.random() per call, always consumed, then
+        random.choice(top_moves) when it explores -- so a seeded (or monkey-patched) `random` module drives this
+        class the way it drives the reference's."""
         valid = board.get_valid_moves()
         if not valid:
             return None
         eng = self._get_engine()
         diff = self.difficulty if self.difficulty in self.PRESETS else "medium"
-        p = _engine.make_params(1, 1.0, planner_steps=1, difficulty=diff, deterministic=False,
-                                seed=random.getrandbits(64))
+        p = _engine.make_params(1, 1.0, planner_steps=1, difficulty=diff, deterministic=True)
         p.planner_k, p.planner_alpha, p.planner_explore = \
             self.params["k"], self.params["mix_alpha"], self.params["explore"]
         boards = eng.boards_from_cells(_board_arrays(board)[None], [board.current_player],
                                        [board.get_move_count()])
-        # live board required by the kernel; a finished board falls back to the reference's
-        # "random valid move" branch (bg_planner.py:239-240 / :269)
         self._calls += 1
-        mv = int(eng.planner_move(boards, self.player, p, sim=self._calls & 0x7FFFFFFF)["move"][0].item())
+        r = eng.planner_move(boards, self.player, p)
+        top = [int(m) for m in r["topk"][0].cpu().numpy()[:self.params["k"]] if m >= 0]
+        if not top:                        # bg_planner.py:239-240
+            return random.choice(valid)
+        top_moves = [(m // self.board_size, m % self.board_size) for m in top]
+        mv = int(r["move"][0].item())
+        if random.random() < self.params["explore"]:
+            return random.choice(top_moves)
         if mv < 0:
             return random.choice(valid)
         return (mv // self.board_size, mv % self.board_size)

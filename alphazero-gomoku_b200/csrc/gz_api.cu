@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <chrono>
 #include <vector>
 
 #include "gz_engine.h"
@@ -101,6 +102,7 @@ extern "C" int gz_create(const gz_config *cfg, gz_handle *out) {
     CK(dalloc(&e->tmp_u8, G * 232));
     CK(dalloc(&e->io_cv, G * kCells)); CK(dalloc(&e->io_cval, G * kCells)); CK(dalloc(&e->io_best, G));
     CK(dalloc(&e->counters, 8));
+    CK(dalloc(&e->d_sim, 4));
     CK(dalloc(&e->log_table, kLogTableMax));
     CK(dalloc(&e->tanh_table, kTanhTableMax));
     *out = reinterpret_cast<gz_handle>(e);
@@ -119,7 +121,7 @@ extern "C" int gz_destroy(gz_handle h) {
                     t.prior, t.n_nodes, t.root, t.ai_player, e->sim.board, e->sim.leaf,
                     e->sim.need_eval, e->sim.steps, e->sim.value, e->sim.topk, e->sim.ntop, e->act[0],
                     e->act[1], e->act[2], e->gn_logits, e->gn_policy, e->dqn_q, e->pv_logits,
-                    e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->log_table,
+                    e->pv_probs, e->pv_value, e->tmp_boards, e->tmp_u8, e->io_cv, e->io_cval, e->io_best, e->counters, e->d_sim, e->log_table,
                     e->tanh_table, e->weight_blob, e->planes[0], e->planes[1], e->planes[2], e->bw.pv_blob, e->bw.gn_blob, e->bw.dqn_w, e->bw.dqn_bias, e->bw.pv_head_blob, e->bw.gn_head_blob, e->pv_pc, e->pv_vc, e->gn_pc, e->pv.conv0.w, e->gn.embed.w, e->dqn.w1t};
     for (void *p : ptrs) if (p) cudaFree(p);
     sp_free(e);
@@ -448,6 +450,7 @@ static SearchCfg make_cfg(const gz_search_params *p) {
     c.seed_lo = (uint32_t)(p->seed & 0xFFFFFFFFull);
     c.seed_hi = (uint32_t)(p->seed >> 32);
     c.game_base = p->game_base;
+    c.d_sim = nullptr;
     return c;
 }
 
@@ -630,6 +633,7 @@ static Engine *lane_view(Engine *e, int l, size_t g0) {
     v->pv = e->pv; v->gn = e->gn; v->dqn = e->dqn; v->bw = e->bw;
     v->log_table = e->log_table; v->tanh_table = e->tanh_table; v->n_log = e->n_log; v->n_tanh = e->n_tanh;
     v->counters = e->counters;
+    v->d_sim = e->d_sim;
     const size_t cap = e->tree.cap, n0 = g0 * cap;
     const TreeArrays &t = e->tree;
     v->tree = {t.cap, t.parent + n0, t.move + n0, t.status + n0, t.nchild + n0, t.nempty + n0,
@@ -651,15 +655,13 @@ static Engine *lane_view(Engine *e, int l, size_t g0) {
     return v;
 }
 
-static void search_lane(Engine *v, const gz_board *d_boards, const uint8_t *d_ai, int G, SearchCfg c,
-                        int32_t *d_cv, double *d_cval, int32_t *d_best, cudaStream_t s) {
+static void search_lane(Engine *v, const gz_board *d_boards, const uint8_t *d_ai, int G, SearchCfg c, cudaStream_t s) {
     prof_begin(*v, GZ_STAGE_TREE, 1, s);
     launch_tree_init(*v, d_boards, d_ai, G, s);
     prof_end(*v, s);
     if (c.eval_nodes)
         nn_pv_forward(*v, v->sim.board, v->sim.need_eval, G, nullptr, nullptr, nullptr, v->tree.prior,
                       v->sim.leaf, s);
-    (void)d_cv; (void)d_cval; (void)d_best;
 }
 
 static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_ai, int G,
@@ -686,21 +688,77 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
         lc[l] = c;
         lc[l].game_base = c.game_base + (uint32_t)g0[l];   // Philox streams keyed by the global game id
         if (nl > 1) CK(cudaStreamWaitEvent(ls[l], e->lane_go, 0));
-        search_lane(v[l], d_boards + g0[l], d_ai + g0[l], g0[l + 1] - g0[l], lc[l], nullptr, nullptr, nullptr, ls[l]);
+        search_lane(v[l], d_boards + g0[l], d_ai + g0[l], g0[l + 1] - g0[l], lc[l], ls[l]);
     }
-    // waves are issued lane by lane so that the lanes' kernels interleave in the hardware queues
-    for (int sim = 0; sim < c.S; ++sim) {
+    // One wave = one simulation of every tree: select/expand (+ backup of the previous wave), policy-value forward of
+    // the new nodes, planner-guided playouts.  Waves are issued lane by lane so that the lanes' kernels interleave in
+    // the hardware queues.
+    auto wave = [&](int sim, const SearchCfg *cfgs) {
         for (int l = 0; l < nl; ++l) {
             const int n = g0[l + 1] - g0[l];
             prof_begin(*v[l], GZ_STAGE_TREE, 1, ls[l]);
-            launch_tree_step(*v[l], n, lc[l], sim, ls[l]);
+            launch_tree_step(*v[l], n, cfgs[l], sim, ls[l]);
             prof_end(*v[l], ls[l]);
             if (c.eval_nodes)
                 nn_pv_forward(*v[l], v[l]->sim.board, v[l]->sim.need_eval, n, nullptr, nullptr, nullptr,
                               v[l]->tree.prior, v[l]->sim.leaf, ls[l]);
-            run_playouts(v[l], n, lc[l], sim, ls[l]);
+            run_playouts(v[l], n, cfgs[l], sim, ls[l]);
+        }
+    };
+    // AlphaZeroGomokuAI.time_limit (ai_agent.py:183-189): checked on the host every kTimeCheckWaves waves
+    const bool timed = p->time_limit_s > 0.0 && std::isfinite(p->time_limit_s);
+    const auto t_start = std::chrono::steady_clock::now();
+    constexpr int kTimeCheckWaves = 4;
+    auto out_of_time = [&]() -> bool {
+        for (int l = 0; l < nl; ++l) cudaStreamSynchronize(ls[l]);
+        return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count() > p->time_limit_s;
+    };
+    int done = 0;   // simulations started
+    // Small batches are launch-bound (~50 kernels per wave, microseconds of work each: AlphaZeroGomokuAI.get_move on
+    // one board): wave 0 runs eagerly, one wave is captured into a CUDA graph whose kernels read the simulation index
+    // from device memory, and the graph is replayed for the remaining simulations.
+    const bool graphed = nl == 1 && !e->profiling && G <= kGraphMaxGames && c.S >= 4 && !e->no_graph;
+    if (graphed) {
+        wave(0, lc);
+        done = 1;
+        SearchCfg gc = lc[0];
+        gc.d_sim = e->d_sim;
+        launch_set_sim(e->d_sim, 1, 0, s);
+        e->launches += 1;
+        const int64_t before = e->launches;
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        wave(-1, &gc);
+        launch_set_sim(e->d_sim, 1, 1, s);
+        cudaError_t ce = cudaStreamEndCapture(s, &graph);
+        if (ce != cudaSuccess) return fail(GZ_ERR_CUDA, "gz_search: graph capture: %s", cudaGetErrorString(ce));
+        const int64_t per_wave = e->launches - before + 1;   // + the set_sim node
+        e->launches = before;                                // nothing ran during the capture
+        ce = cudaGraphInstantiate(&exec, graph, 0);
+        if (ce != cudaSuccess) { cudaGraphDestroy(graph); return fail(GZ_ERR_CUDA, "gz_search: graph instantiate: %s", cudaGetErrorString(ce)); }
+        for (int sim = 1; sim < c.S; ++sim) {
+            if (timed && sim % kTimeCheckWaves == 0 && out_of_time()) break;
+            ce = cudaGraphLaunch(exec, s);
+            if (ce != cudaSuccess) break;
+            e->launches += per_wave;
+            done = sim + 1;
+        }
+        cudaGraphExecDestroy(exec);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) return fail(GZ_ERR_CUDA, "gz_search: graph launch: %s", cudaGetErrorString(ce));
+    } else {
+        for (int sim = 0; sim < c.S; ++sim) {
+            if (timed && sim > 0 && sim % kTimeCheckWaves == 0 && out_of_time()) break;
+            wave(sim, lc);
+            done = sim + 1;
         }
     }
+    if (done < c.S) {   // cut short by the time limit: the closing launch below backs up simulation done - 1 and stops
+        c.S = done;
+        for (int l = 0; l < nl; ++l) lc[l].S = done;
+    }
+    e->last_simulations = done;
     for (int l = 0; l < nl; ++l) {
         const int n = g0[l + 1] - g0[l];
         prof_begin(*v[l], GZ_STAGE_TREE, 2, ls[l]);
@@ -726,11 +784,7 @@ extern "C" int gz_search(gz_handle h, const gz_board *d_boards, const uint8_t *d
     int rc = check_batch(e, G, "gz_search");
     if (rc) return rc;
     if (!d_boards || !d_ai_player || !p) return fail(GZ_ERR_ARG, "gz_search: null pointer");
-    rc = search_device(e, d_boards, d_ai_player, G, p, d_child_visits, d_child_value, d_best_move, strm(stream));
-    if (rc) return rc;
-    unsigned long long add = (unsigned long long)G * (unsigned long long)p->num_simulations;
-    (void)add;
-    return GZ_OK;
+    return search_device(e, d_boards, d_ai_player, G, p, d_child_visits, d_child_value, d_best_move, strm(stream));
 }
 
 extern "C" int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t *h_to_move,
@@ -885,6 +939,16 @@ extern "C" int gz_selfplay_step(gz_handle h, void *stream) {
     return GZ_OK;
 }
 
+extern "C" int gz_selfplay_set_simulations(gz_handle h, int32_t n) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_selfplay_set_simulations: null handle");
+    if (e->sp_G < 1 || e->sp_cfg.arena != 0) return fail(GZ_ERR_STATE, "gz_selfplay_set_simulations: no self-play session");
+    if (n < 1 || n > e->cfg.max_simulations) return fail(GZ_ERR_ARG, "gz_selfplay_set_simulations: out of range");
+    e->sp_params.num_simulations = n;
+    e->sp_cfg.sims_a = e->sp_cfg.sims_b = n;
+    return GZ_OK;
+}
+
 extern "C" int gz_selfplay_drain(gz_handle h, gz_replay_record *d_out, int64_t cap, int64_t *h_n, void *stream) {
     Engine *e = eng(h);
     if (!e || !h_n) return fail(GZ_ERR_ARG, "gz_selfplay_drain: null argument");
@@ -952,6 +1016,26 @@ extern "C" int gz_get_tree(gz_handle h, int32_t g, int32_t cap, int32_t *h_paren
     return GZ_OK;
 }
 
+extern "C" int gz_get_priors(gz_handle h, int32_t g, int32_t node, float *h_prior, float *h_value) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_get_priors: null handle");
+    if (!e->searched) return fail(GZ_ERR_STATE, "gz_get_priors: no search has run on this handle");
+    if (!e->tree.prior) return fail(GZ_ERR_STATE, "gz_get_priors: the handle was created without store_priors");
+    if (g < 0 || g >= e->cfg.max_games) return fail(GZ_ERR_ARG, "gz_get_priors: game index out of range");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaDeviceSynchronize());
+    int nn = 0;
+    CK(cudaMemcpy(&nn, e->tree.n_nodes + g, sizeof(int), cudaMemcpyDeviceToHost));
+    if (node < 0 || node >= nn) return fail(GZ_ERR_ARG, "gz_get_priors: node index out of range");
+    const size_t slot = (size_t)g * e->tree.cap + node;
+    uint8_t st = 0;
+    CK(cudaMemcpy(&st, e->tree.status + slot, 1, cudaMemcpyDeviceToHost));
+    if (st != 0) return fail(GZ_ERR_STATE, "gz_get_priors: terminal nodes have no prior (ai_agent.py:522)");
+    if (h_prior) CK(cudaMemcpy(h_prior, e->tree.prior + slot * kPolicyPitch, kCells * sizeof(float), cudaMemcpyDeviceToHost));
+    if (h_value) CK(cudaMemcpy(h_value, e->tree.vhead + slot, sizeof(float), cudaMemcpyDeviceToHost));
+    return GZ_OK;
+}
+
 extern "C" int gz_get_counters(gz_handle h, gz_counters *out) {
     Engine *e = eng(h);
     if (!e || !out) return fail(GZ_ERR_ARG, "gz_get_counters: null argument");
@@ -966,6 +1050,7 @@ extern "C" int gz_get_counters(gz_handle h, gz_counters *out) {
     out->terminal_leaves = (int64_t)c[5];
     out->simulations = (int64_t)c[0];
     out->kernel_launches = e->launches;
+    out->last_search_simulations = e->last_simulations;
     return GZ_OK;
 }
 
@@ -1008,6 +1093,13 @@ extern "C" int gz_set_profiling(gz_handle h, int32_t on) {
     Engine *e = eng(h);
     if (!e) return fail(GZ_ERR_ARG, "gz_set_profiling: null handle");
     e->profiling = on != 0;
+    return GZ_OK;
+}
+
+extern "C" int gz_set_graph(gz_handle h, int32_t on) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_set_graph: null handle");
+    e->no_graph = on == 0;
     return GZ_OK;
 }
 

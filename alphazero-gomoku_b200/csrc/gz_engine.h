@@ -112,6 +112,8 @@ struct SimArrays {
 };
 
 constexpr int kMaxLanes = 4;
+// gz_search replays its waves from a CUDA graph when the batch is at most this many games (launch-bound regime)
+constexpr int kGraphMaxGames = 256;
 
 // ---- self-play state (gz_kernels_selfplay.cu) ---------------------------------------------------
 constexpr int kMaxPlies = 200;     // a game ends at the 200th stone at the latest (gomoku_board.py:106)
@@ -179,8 +181,11 @@ struct Engine {
     double *io_cval;      // [G][225]
     int32_t *io_best;     // [G]
     unsigned long long *counters; // device gz_counters-shaped
+    int32_t *d_sim;       // simulation index of the wave in flight when waves are replayed from a CUDA graph
     int64_t launches;     // host-side launch counter
     bool searched;
+    bool no_graph;        // gz_set_graph(0): never replay waves from a CUDA graph
+    int32_t last_simulations;   // simulations per tree of the last search (< num_simulations when the time limit cut it)
     // optional stage timing with CUDA events on the launching stream (gz_set_profiling)
     bool profiling;
     std::vector<cudaEvent_t> ev_pool;
@@ -199,6 +204,8 @@ struct SearchCfg {
     int32_t planner_steps, planner_k, deterministic, eval_nodes;
     double c_puct, beta, alpha, explore;
     uint32_t seed_lo, seed_hi, game_base;
+    // simulation index read from device memory instead of the launch argument (waves replayed from a CUDA graph)
+    const int32_t *d_sim;
 };
 
 // ---- launchers -------------------------------------------------------------------------------
@@ -233,6 +240,7 @@ void launch_tree_init(const Engine &e, const gz_board *boards, const uint8_t *ai
 void launch_tree_step(const Engine &e, int G, const SearchCfg &c, int sim, cudaStream_t s);
 void launch_tree_finalize(const Engine &e, int G, const SearchCfg &c, int32_t *child_visits,
                           double *child_value, int32_t *best_move, cudaStream_t s);
+void launch_set_sim(int32_t *d_sim, int value, int add, cudaStream_t s);   // *d_sim = add ? *d_sim + value : value
 
 // self-play kernels (gz_kernels_selfplay.cu)
 void launch_sp_begin(const SelfPlayArrays &sp, int G, const SelfPlayCfg &c, cudaStream_t s);

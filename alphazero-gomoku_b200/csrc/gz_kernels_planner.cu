@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
 // for them).  Lane 0 of the group then rolls the explore dice and plays the move.
 __global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boards,
                                                       int32_t *__restrict__ steps, int G, SearchCfg c,
-                                                      int sim, int step_override,
+                                                      int sim_arg, int step_override,
                                                       const int32_t *__restrict__ topk,
                                                       const int32_t *__restrict__ ntop,
                                                       const float *__restrict__ policy,
@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(128) k_planner_pick(gz_board *__restrict__ boa
     static_assert(kMaxTopK == 16, "one lane per candidate");
     const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 4;
     const int sub = threadIdx.x & 15;
+    const int sim = c.d_sim ? *c.d_sim : sim_arg;
     const bool in_range = g < G;
     const int gi = in_range ? g : G - 1;
     int did = 0;

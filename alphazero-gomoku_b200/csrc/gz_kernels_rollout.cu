@@ -96,9 +96,10 @@ __device__ __forceinline__ int g_count(uint32_t w) {
 __global__ void __launch_bounds__(128) k_rollout_tail(gz_board *__restrict__ boards,
                                                       const uint8_t *__restrict__ ai_player,
                                                       int32_t *__restrict__ steps, int G, SearchCfg c,
-                                                      int sim, double *__restrict__ value,
+                                                      int sim_arg, double *__restrict__ value,
                                                       unsigned long long *__restrict__ counters) {
     const int lane = threadIdx.x & 31;
+    const int sim = c.d_sim ? *c.d_sim : sim_arg;
     GroupCtx g;
     g.j = lane & 7;
     g.gmask = 0xFFu << (lane & 24);

@@ -92,14 +92,17 @@ __device__ __forceinline__ double ucb1(double value, int visits, double num, dou
     return __dadd_rn(__dadd_rn(exploitation, exploration), bgb);
 }
 
+__global__ void k_set_sim(int32_t *d_sim, int value, int add) { *d_sim = add ? *d_sim + value : value; }
+
 __global__ void __launch_bounds__(128) k_tree_step(TreeArrays t, SimArrays sm, int G, SearchCfg c,
-                                                   int sim, const double *__restrict__ log_table,
+                                                   int sim_arg, const double *__restrict__ log_table,
                                                    int n_log, const double *__restrict__ tanh_table,
                                                    int n_tanh,
                                                    unsigned long long *__restrict__ counters) {
     int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (g >= G) return;
+    const int sim = c.d_sim ? *c.d_sim : sim_arg;
     NodeView v = node_view(t, g);
     // ---- backup of the previous simulation (:441-448), same sign on the whole path
     if (sim > 0) {
@@ -225,6 +228,7 @@ void launch_tree_step(const Engine &e, int G, const SearchCfg &c, int sim, cudaS
     k_tree_step<<<(G * 32 + 127) / 128, 128, 0, s>>>(e.tree, e.sim, G, c, sim, e.log_table, e.n_log,
                                                      e.tanh_table, e.n_tanh, e.counters);
 }
+void launch_set_sim(int32_t *d_sim, int value, int add, cudaStream_t s) { k_set_sim<<<1, 1, 0, s>>>(d_sim, value, add); }
 void launch_tree_finalize(const Engine &e, int G, const SearchCfg &c, int32_t *child_visits,
                           double *child_value, int32_t *best_move, cudaStream_t s) {
     (void)c;

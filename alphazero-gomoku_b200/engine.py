@@ -23,7 +23,7 @@ EXPORTS = [
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
     "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_set_lanes", "gz_get_stage_times", "gz_debug_pv_layer",
     "gz_selfplay_begin", "gz_selfplay_step", "gz_selfplay_drain", "gz_selfplay_boards", "gz_selfplay_get_stats",
-    "gz_dataset_build", "gz_arena_begin", "gz_arena_get_stats",
+    "gz_dataset_build", "gz_arena_begin", "gz_arena_get_stats", "gz_get_priors", "gz_set_graph", "gz_selfplay_set_simulations",
 ]
 
 ARENA_ENGINE, ARENA_RANDOM = 1, 2     # GZ_ARENA_ENGINE / GZ_ARENA_RANDOM
@@ -41,12 +41,14 @@ class GzSearchParams(C.Structure):
     _fields_ = [("num_simulations", C.c_int32), ("planner_steps", C.c_int32),
                 ("planner_k", C.c_int32), ("deterministic", C.c_int32), ("c_puct", C.c_double),
                 ("beta", C.c_double), ("planner_alpha", C.c_double), ("planner_explore", C.c_double),
-                ("seed", C.c_uint64), ("game_base", C.c_uint32), ("eval_nodes", C.c_int32)]
+                ("seed", C.c_uint64), ("game_base", C.c_uint32), ("eval_nodes", C.c_int32),
+                ("time_limit_s", C.c_double)]
 
 
 class GzCounters(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("simulations", "nodes_created", "pv_evals", "planner_steps",
-                                          "rollout_steps", "terminal_leaves", "kernel_launches")]
+                                          "rollout_steps", "terminal_leaves", "kernel_launches",
+                                          "last_search_simulations")]
 
 
 class GzSelfplayStats(C.Structure):
@@ -97,11 +99,12 @@ def flatten_state_dict(sd):
 
 
 def make_params(sims, c_puct, beta=0.2, planner_steps=0, difficulty="medium", deterministic=False,
-                seed=0, game_base=0, eval_nodes=True):
+                seed=0, game_base=0, eval_nodes=True, time_limit=0.0):
     k, a, e = PLANNER_PRESETS.get(difficulty, PLANNER_PRESETS["medium"])
     return GzSearchParams(int(sims), int(max(0, planner_steps)), k, int(bool(deterministic)),
                           float(c_puct), float(beta), a, e, int(seed) & (2 ** 64 - 1),
-                          int(game_base), int(bool(eval_nodes)))
+                          int(game_base), int(bool(eval_nodes)),
+                          float(time_limit) if time_limit and time_limit != float("inf") else 0.0)
 
 
 def _ptr(t):
@@ -320,6 +323,9 @@ class Engine:
     def selfplay_step(self):
         self._ck(self.L.gz_selfplay_step(self.h, self._stream()))
 
+    def selfplay_set_simulations(self, n):
+        self._ck(self.L.gz_selfplay_set_simulations(self.h, int(n)))
+
     def selfplay_stats(self):
         st = GzSelfplayStats()
         self._ck(self.L.gz_selfplay_get_stats(self.h, C.byref(st)))
@@ -382,6 +388,14 @@ class Engine:
         k = n.value
         return dict(parent=parent[:k], move=move[:k], visits=visits[:k], value=value[:k])
 
+    def get_priors(self, g, node=0):
+        """(MCTSNode.prior_prob as float32[225] over raster cells (0 on occupied cells), value-head output) of a
+        node of game g after a search; needs store_priors=True."""
+        pr = np.empty(225, np.float32)
+        v = C.c_float()
+        self._ck(self.L.gz_get_priors(self.h, int(g), int(node), pr.ctypes.data_as(C.c_void_p), C.byref(v)))
+        return pr, v.value
+
     def counters(self):
         c = GzCounters()
         self._ck(self.L.gz_get_counters(self.h, C.byref(c)))
@@ -389,6 +403,9 @@ class Engine:
 
     def set_profiling(self, on):
         self._ck(self.L.gz_set_profiling(self.h, int(bool(on))))
+
+    def set_graph(self, on):
+        self._ck(self.L.gz_set_graph(self.h, int(bool(on))))
 
     def set_lanes(self, lanes):
         self._ck(self.L.gz_set_lanes(self.h, int(lanes)))

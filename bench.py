@@ -2,7 +2,8 @@
 """Benchmark of the MCTS hot path (BASELINE.json metric: MCTS simulations/s, 15x15, "hard").
 
     python bench.py --gpus N --steps K --warmup W            # the B200 engine
-    python bench.py --impl reference --steps K --warmup W    # the CPU baseline arm (oracle port)
+    python bench.py --impl reference --steps K --warmup W    # the CPU arm: the unmodified Python reference from
+                                                             # baseline/_ref (one process per core), else the C port
 
 A step = one search pass (gz_search) over one batch of G synthetic positions: S simulations per
 position, each simulation = select + expand + policy-value forward of the new node + planner-guided
@@ -169,40 +170,204 @@ def config_dict(G, n_gpus, extra=None):
     return c
 
 
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+REF_FILES = ("gomoku_board.py", "ai_agent.py", "bg_planner.py", "neural_network.py")
+
+
+def reference_available():
+    return all(os.path.exists(os.path.join(REF_DIR, f)) for f in REF_FILES)
+
+
+class _StopSearch(Exception):
+    pass
+
+
+def _ref_worker(w, nw, counter, ready, stop, sims_per_search):
+    """One process = one core: the UNMODIFIED reference (baseline/_ref/{gomoku_board,ai_agent,bg_planner,
+    neural_network}.py, copied there by __graft_entry__.build()) running AlphaZeroGomokuAI._mcts_search with the
+    workload's preset on a spread of the workload positions.  Hygiene per SURVEY.md 8c: scratch cwd without ./models,
+    time_limit = inf, one torch thread, params overridden through ai.params (training.py:240).  Nothing of the
+    reference is modified: completed simulations are counted by wrapping the bound method _mcts_simulation."""
+    import importlib.util
+    import tempfile
+    os.chdir(tempfile.mkdtemp(prefix="gz_ref_"))
+    pkg = os.path.join(ROOT, "alphazero-gomoku_b200")
+    spec = importlib.util.spec_from_file_location("gz_workload", os.path.join(pkg, "workload.py"))
+    workload = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(workload)
+    sys.path[:] = [REF_DIR] + [p for p in sys.path if os.path.abspath(p or ".") != pkg]
+    import torch
+    torch.set_num_threads(1)
+    torch.manual_seed(1234)
+    import ai_agent
+    from gomoku_board import GomokuBoard
+    assert os.path.dirname(os.path.abspath(ai_agent.__file__)) == REF_DIR
+    cells, tm, mc = workload.make_positions(256, seed=2026)
+    order = np.random.default_rng(7).permutation(256)        # every worker sees every stone count
+    ais = {}
+    for player in (1, 2):
+        ai = ai_agent.AlphaZeroGomokuAI(player, "hard", device="cpu", beta=PRESET["beta"],
+                                        planner_steps=PRESET["planner_steps"], time_limit=float("inf"))
+        ai.params["num_simulations"] = sims_per_search
+        ai.params["c_puct"] = PRESET["c_puct"]
+        inner = ai._mcts_simulation
+
+        def counted(root, _inner=inner):
+            if stop.is_set():
+                raise _StopSearch()
+            _inner(root)
+            with counter.get_lock():
+                counter.value += 1
+        ai._mcts_simulation = counted
+        ais[player] = ai
+    ready.set()
+    k = w
+    try:
+        while not stop.is_set():
+            i = int(order[k % 256])
+            k += nw
+            b = GomokuBoard()
+            c = cells[i].reshape(15, 15)
+            b.board = c.astype(b.board.dtype)
+            blk = [(int(r), int(q), 1) for r, q in zip(*np.nonzero(c == 1))]
+            wht = [(int(r), int(q), 2) for r, q in zip(*np.nonzero(c == 2))]
+            b.move_history = [x for pair in zip(blk, wht) for x in pair] + blk[len(wht):]
+            b.current_player = int(tm[i])
+            ais[int(tm[i])]._mcts_search(b, b.get_valid_moves())
+    except _StopSearch:
+        pass
+
+
+class ReferencePool:
+    """os.cpu_count() worker processes running the Python reference; window(seconds) returns the simulations all of
+    them completed in that wall-clock window."""
+
+    def __init__(self, sims_per_search=2, workers=None):
+        import multiprocessing as mp
+        ctx = mp.get_context("spawn")
+        self.n = workers or os.cpu_count() or 1
+        self.stop = ctx.Event()
+        self.counters = [ctx.Value("q", 0) for _ in range(self.n)]
+        readies = [ctx.Event() for _ in range(self.n)]
+        self.procs = [ctx.Process(target=_ref_worker, args=(w, self.n, self.counters[w], readies[w], self.stop,
+                                                            sims_per_search), daemon=True) for w in range(self.n)]
+        for p in self.procs:
+            p.start()
+        for r, p in zip(readies, self.procs):
+            while not r.wait(1.0):
+                if not p.is_alive():
+                    raise RuntimeError("reference worker died during start-up")
+
+    def total(self):
+        return sum(c.value for c in self.counters)
+
+    def window(self, seconds):
+        n0, t0 = self.total(), time.perf_counter()
+        time.sleep(seconds)
+        return self.total() - n0, time.perf_counter() - t0
+
+    def close(self):
+        self.stop.set()
+        for p in self.procs:
+            p.join(timeout=20)
+            if p.is_alive():
+                p.terminate()
+
+
 def run_reference(args):
-    """CPU arm: the reference's algorithm (oracle port) on all host cores; each step = one bounded
-    sample of the same workload."""
+    """CPU arm.  With baseline/_ref present: the reference's own Python code, one process per host core, each step a
+    wall-clock window of --ref-step-seconds in which the workers keep running 2-simulation searches of the same
+    preset over the workload positions (kind "reference"); the C port on all host threads is reported beside it as
+    `optimised_cpu`.  Without baseline/_ref the port alone is timed (kind "port")."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import workload
     cells, tm, mc = workload.make_positions(256, seed=2026)
     sims_ref = 2
-    threads = os.cpu_count() or 1
-    for _ in range(args.warmup):
-        cpu_sample(cells, tm, mc, 0, sims_ref, threads, fixed_searches=1)
-    total, t_all = 0, 0.0
-    for _ in range(args.steps):
-        rate, th, n, dt = cpu_sample(cells, tm, mc, 0, sims_ref, threads, fixed_searches=2)
-        total += n
-        t_all += dt
-    value = total / t_all
-    sample = "%d threads x 2 searches x %d sims per step on the first positions of the workload" % (threads, sims_ref)
+    threads = args.ref_workers or os.cpu_count() or 1
+    extra = {}
+    if reference_available() and not args.port_only:
+        pool = ReferencePool(sims_ref, threads)
+        try:
+            for _ in range(args.warmup):
+                pool.window(args.ref_step_seconds)
+            total, t_all = 0, 0.0
+            for _ in range(args.steps):
+                n, dt = pool.window(args.ref_step_seconds)
+                total += n
+                t_all += dt
+        finally:
+            pool.close()
+        kind = "reference"
+        sample = ("%d processes (one per core, torch 1 thread each) running the unmodified reference's _mcts_search "
+                  "(%d-simulation searches, time_limit=inf) over a fixed shuffle of 256 workload positions; a step = a "
+                  "%.1f s wall-clock window, simulations counted as they complete" % (threads, sims_ref,
+                                                                                     args.ref_step_seconds))
+        rate, th, n_port, dt_port = cpu_sample(cells, tm, mc, min(args.cpu_seconds, 8.0), sims_ref, threads)
+        extra["optimised_cpu"] = {"value": rate, "unit": "sims/s", "cores": th, "kind": "port",
+                                  "sample": "C restatement (oracle/), %d sims in %.1f s" % (n_port, dt_port)}
+    else:
+        for _ in range(args.warmup):
+            cpu_sample(cells, tm, mc, 0, sims_ref, threads, fixed_searches=1)
+        total, t_all = 0, 0.0
+        for _ in range(args.steps):
+            rate, th, n, dt = cpu_sample(cells, tm, mc, 0, sims_ref, threads, fixed_searches=2)
+            total += n
+            t_all += dt
+        kind = "port"
+        sample = ("baseline/_ref absent: C port; %d threads x 2 searches x %d sims per step on the first positions of "
+                  "the workload" % (threads, sims_ref))
+    value = total / max(t_all, 1e-9)
     line = {"impl": "reference", "metric": "mcts_sims_per_sec", "value": value, "unit": "sims/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t_all / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(args.games, args.gpus, {"note": "CPU arm: bounded sample per step"}),
-            "cpu_baseline": {"value": value, "unit": "sims/s", "cores": threads, "kind": "port",
-                             "sample": sample},
+            "config": config_dict(args.games, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "sims/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "sims/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    line.update(extra)
     emit(json.dumps(line))
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's main kernel, from the committed
-# `ncu --set full` capture (profiles/r01_gn_block_ncu_full.md: k_gn_block, 4096 boards: 151.1 MB + 87.6 MB;
-# algorithmic 151.0 MB in + 151.0 MB out, part of the output still sits in L2 when the kernel ends)
-NCU_TRAFFIC = {"gn_convs": 238.7e6}
+def ncu_traffic(stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's main kernel, from the committed
+    `ncu --set full` capture of this round (profiles/ncu_traffic.json: written by profiles/ncu_key_metrics.py from the
+    .ncu-rep of the same bench command); None when no capture is on record for the stage."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f).get(stage, {}).get("bytes_per_launch")
+    except Exception:
+        return None
+
+
+def steady_selfplay(eng, G, rank, warm_plies, window_plies, torch):
+    """BASELINE's second metric inside the same run: hard-preset self-play with game recycling.  Warm start: the G
+    games are first spread over all ages with `warm_plies` cheap plies (8 simulations per move, same engine, same
+    rules) so that slots finish and recycle at different times; then the budget goes back to S = 200 and
+    `window_plies` plies (>= one mean game) are timed.  Returns (milliseconds, stats delta, counters delta)."""
+    import engine
+    p = engine.make_params(8, PRESET["c_puct"], beta=PRESET["beta"], planner_steps=PRESET["planner_steps"],
+                           difficulty=PRESET["difficulty"], deterministic=False, seed=4242, game_base=rank * G)
+    eng.selfplay_begin(G, p, 0.01)        # hard preset: exploration 0.01 (ai_agent.py:84-90)
+    for _ in range(warm_plies):
+        eng.selfplay_step()
+    eng.selfplay_drain()
+    eng.selfplay_set_simulations(PRESET["sims"])
+    for _ in range(3):
+        eng.selfplay_step()
+    torch.cuda.synchronize()
+    st0, c0 = eng.selfplay_stats(), eng.counters()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for k in range(window_plies):
+        eng.selfplay_step()
+        if k % 32 == 31:
+            eng.selfplay_drain()
+    ev1.record()
+    torch.cuda.synchronize()
+    st1, c1 = eng.selfplay_stats(), eng.counters()
+    return ev0.elapsed_time(ev1), {k: st1[k] - st0[k] for k in st1}, {k: c1[k] - c0[k] for k in c1}
 
 
 def run_engine(args):
@@ -218,8 +383,9 @@ def run_engine(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     G, S = args.games, PRESET["sims"]
-    eng = engine.Engine(max_games=G, max_simulations=S, device=local, store_priors=True,
-                        precision=1 if args.precision == "bf16" else 0, lanes=args.lanes)
+    S_CODE = 400                                   # the code's own "hard" preset (ai_agent.py:84-90)
+    eng = engine.Engine(max_games=G, max_simulations=S_CODE if args.s400_steps else S, device=local,
+                        store_priors=True, precision=1 if args.precision == "bf16" else 0, lanes=args.lanes)
     pv, gn, dq = synthetic_weights()
     eng.set_pv_weights(pv)
     eng.set_planner_weights(gn, dq)
@@ -227,8 +393,8 @@ def run_engine(args):
     boards = eng.boards_from_cells(cells, tm, mc)
     ai = tm.copy()
 
-    def params(step):
-        return engine.make_params(S, PRESET["c_puct"], beta=PRESET["beta"],
+    def params(step, sims=S):
+        return engine.make_params(sims, PRESET["c_puct"], beta=PRESET["beta"],
                                   planner_steps=PRESET["planner_steps"], difficulty=PRESET["difficulty"],
                                   deterministic=False, seed=0xB200 + step, game_base=rank * G)
 
@@ -238,12 +404,23 @@ def run_engine(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    def reduce_max(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    def reduce_sum(x):
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t.item()
+
+    # ---- the timed region: K searches, inputs resident in HBM, no instrumentation inside
     for w in range(args.warmup):
         eng.search(boards, ai, params(1000 + w))
     barrier()
     eng.reset_counters()
-    eng.set_profiling(True)
-    eng.stage_times()
     sampler = ClockSampler(local)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -254,15 +431,8 @@ def run_engine(args):
     barrier()
     ms = ev0.elapsed_time(ev1)
     clocks = sampler.finish()
-    stages = eng.stage_times()
-    eng.set_profiling(False)
     cnt = eng.counters()
-    t_ms = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    sims = torch.tensor([float(cnt["simulations"])], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(sims, op=dist.ReduceOp.SUM)
-    ms_max, sims_total = t_ms.item(), sims.item()
+    ms_max, sims_total = reduce_max(ms), reduce_sum(cnt["simulations"])
     value = sims_total / (ms_max / 1e3)
 
     # ---- end to end through the host-buffer entry point (pinned host memory, copies timed)
@@ -275,24 +445,55 @@ def run_engine(args):
     for k in range(args.steps):
         eng.search_host(h_cells, h_tm, h_mc, h_ai, params(3000 + k), out)
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t_e = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-    e2e = world * G * S * args.steps / t_e.item()
+    e2e_s = reduce_max(time.perf_counter() - t0)
+    e2e = world * G * S * args.steps / e2e_s
     h2d = G * (225 + 1 + 1 + 2)
     d2h = G * (225 * 4 + 225 * 8 + 4)
 
-    # ---- one more step with every kernel on one stream: per-launch times free of lane overlap
+    # ---- one extra step with stage events on (every kernel on one stream): where the time goes, and the roofline of
+    #      the dominant kernel.  The ~19 k event records it needs stay out of the timed region above.
     eng.set_lanes(1)
     eng.reset_counters()
     eng.set_profiling(True)
     eng.stage_times()
     eng.search(boards, ai, params(5000))
-    serial = eng.stage_times()
-    cnt_serial = eng.counters()
+    stages = eng.stage_times()
+    cnt_stage = eng.counters()
     eng.set_profiling(False)
     eng.set_lanes(args.lanes)
+
+    # ---- the code's own hard preset (S = 400) on the same positions
+    s400 = None
+    if args.s400_steps:
+        eng.search(boards, ai, params(6000, S_CODE))
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for k in range(args.s400_steps):
+            eng.search(boards, ai, params(6100 + k, S_CODE))
+        e1.record()
+        barrier()
+        ms400 = reduce_max(e0.elapsed_time(e1))
+        s400 = {"value": world * G * S_CODE * args.s400_steps / (ms400 / 1e3), "unit": "sims/s",
+                "sims_per_position": S_CODE, "steps": args.s400_steps, "ms_per_step": ms400 / args.s400_steps,
+                "note": "ai_agent.py:84-90 preset (400 simulations, c_puct 1.8); same positions, device-resident"}
+
+    # ---- BASELINE's second metric: self-play games/hour, steady state
+    sp = None
+    if args.selfplay_plies:
+        barrier()
+        sp_ms, sp_st, sp_cnt = steady_selfplay(eng, G, rank, args.selfplay_warm, args.selfplay_plies, torch)
+        t_sp = reduce_max(sp_ms) / 1e3
+        games, plies = reduce_sum(sp_st["games_finished"]), reduce_sum(sp_st["plies_played"])
+        sp = {"value": games / t_sp * 3600.0, "unit": "games/h", "window_plies": args.selfplay_plies,
+              "warm_start": "%d plies at 8 simulations per move to spread the games over all ages, then 3 plies at "
+                            "S=200 before the window" % args.selfplay_warm,
+              "games_finished": games, "plies_played": plies, "seconds": t_sp,
+              "mean_plies_per_finished_game": plies / games if games else None,
+              "sims_per_sec": reduce_sum(sp_cnt["simulations"]) / t_sp,
+              "records_dropped": reduce_sum(sp_st["records_dropped"]),
+              "config": "hard preset self-play from empty boards with game recycling: S=200, c_puct=1.8, beta=0.2, "
+                        "planner_steps=5, epsilon=0.01, %d concurrent games per GPU" % G}
 
     if rank == 0:
         peaks = load_peaks()
@@ -302,30 +503,22 @@ def run_engine(args):
         share = {k: round(v[0] / total_ms, 4) for k, v in stages.items() if v[1]}
         if dom in STAGE_FLOPS:
             unit, f = STAGE_FLOPS[dom]
-            achieved = cnt[unit] * f / (d_ms / 1e3) / 1e12
+            achieved = cnt_stage[unit] * f / (d_ms / 1e3) / 1e12
             roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"],
-                    "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                    "traffic": NCU_TRAFFIC.get(dom)}
+                    "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"], "traffic": ncu_traffic(dom)}
         else:
             unit, by = STAGE_BYTES.get(dom, ("simulations", 0))
-            achieved = cnt[unit] * by / (d_ms / 1e3) / 1e9
+            achieved = cnt_stage[unit] * by / (d_ms / 1e3) / 1e9
             roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
-                    "frac": achieved / peaks["hbm"], "traffic": None}
-        s_ms, s_launch = serial[dom]
-        if dom in STAGE_FLOPS:
-            s_ach = cnt_serial[STAGE_FLOPS[dom][0]] * STAGE_FLOPS[dom][1] / (s_ms / 1e3) / 1e12
-        else:
-            s_ach = cnt_serial[unit] * by / (s_ms / 1e3) / 1e9
-        roof["serial"] = {"note": "same kernel with lanes=1 (nothing else on the GPU), one extra step after the "
-                                  "timed region", "achieved": s_ach, "frac": s_ach / roof["peak"],
-                          "avg_launch_ms": s_ms / max(s_launch, 1),
-                          "stage_ms": {k: round(v[0], 2) for k, v in serial.items() if v[1]}}
+                    "frac": achieved / peaks["hbm"], "traffic": ncu_traffic(dom)}
         roof.update({"kernel": dom, "launches": d_launch, "avg_launch_ms": d_ms / max(d_launch, 1),
                      "share_of_step": round(d_ms / total_ms, 4), "stage_share": share,
+                     "stage_ms": {k: round(v[0], 2) for k, v in stages.items() if v[1]},
+                     "measured": "CUDA events around every kernel group of ONE extra step after the timed region "
+                                 "(gz_set_profiling; every kernel on the launching stream)",
                      "peak_source": peaks["source"] + (" (sustained bf16 cuBLAS)" if roof["bound"] == "tensor" else " (copy)")})
         f_sim = (cnt["pv_evals"] * (F_PV_CONV0 + F_PV_TOWER + F_PV_HEADS) +
                  cnt["planner_steps"] * (F_GN_CONVS + F_GN_HEAD + F_DQN)) / max(cnt["simulations"], 1)
-        cpu_rate, cores, n_cpu, dt_cpu = cpu_sample(cells[:256], tm[:256], mc[:256], args.cpu_seconds, 2)
         line = {"metric": "mcts_sims_per_sec", "value": value, "unit": "sims/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
@@ -334,15 +527,49 @@ def run_engine(args):
                 "e2e": {"value": e2e, "unit": "sims/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
                 "gpu_launches": cnt["kernel_launches"],
                 "roofline": roof,
-                "cpu_baseline": {"value": cpu_rate, "unit": "sims/s", "cores": cores, "kind": "port",
-                                 "sample": "%d sims in %.1f s: %d threads running 2-sim searches of the same "
-                                           "preset on the first 256 workload positions" % (n_cpu, dt_cpu, cores)},
                 "flops_per_sim": f_sim,
                 "tensor_frac_whole_step": value * f_sim / 1e12 / peaks["tf_sustained"] / world,
                 "counters": cnt}
+        if sp:
+            line["selfplay_games_per_hour"] = sp
+        if s400:
+            line["code_preset_s400"] = s400
+        if world == 1:
+            line.update(cpu_legs(args, cells, tm, mc))
         emit(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
+
+
+def cpu_legs(args, cells, tm, mc):
+    """cpu_baseline of the engine line (rank 0, N = 1): the Python reference from baseline/_ref on every host core for
+    --cpu-seconds when it is there (kind "reference"), the C port beside it as optimised_cpu; else the port."""
+    out = {}
+    threads = args.ref_workers or os.cpu_count() or 1
+    port_rate, cores, n_cpu, dt_cpu = cpu_sample(cells[:256], tm[:256], mc[:256],
+                                                 args.cpu_seconds if not reference_available() else min(args.cpu_seconds, 8.0),
+                                                 2, threads)
+    port = {"value": port_rate, "unit": "sims/s", "cores": cores, "kind": "port",
+            "sample": "%d sims in %.1f s: %d threads running 2-sim searches of the same preset on the first 256 "
+                      "workload positions (C restatement, oracle/)" % (n_cpu, dt_cpu, cores)}
+    if reference_available() and not args.port_only:
+        try:
+            pool = ReferencePool(2, threads)
+            try:
+                pool.window(2.0)
+                n, dt = pool.window(args.cpu_seconds)
+            finally:
+                pool.close()
+            out["cpu_baseline"] = {"value": n / dt, "unit": "sims/s", "cores": threads, "kind": "reference",
+                                   "sample": "%d sims in %.1f s: %d processes running the unmodified Python reference's "
+                                             "_mcts_search (2-sim searches, same preset) over a shuffle of 256 workload "
+                                             "positions" % (n, dt, threads)}
+            out["optimised_cpu"] = port
+            return out
+        except Exception as exc:          # the arm must not take the GPU line down with it
+            port["sample"] += "; Python reference arm failed: %r" % (exc,)
+    out["cpu_baseline"] = port
+    return out
 
 
 def selfplay_session(eng, G, rank, seed=2026):
@@ -620,6 +847,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--games", type=int, default=4096)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--ref-step-seconds", type=float, default=4.0,
+                    help="--impl reference: wall-clock window of one step of the Python reference arm")
+    ap.add_argument("--ref-workers", type=int, default=0, help="CPU legs: worker processes / threads (0 = all cores)")
+    ap.add_argument("--port-only", action="store_true", help="CPU legs: time the C port even if baseline/_ref exists")
     ap.add_argument("--lanes", type=int, default=0,
                     help="independent game groups advanced on separate CUDA streams (0 = engine default)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
@@ -628,6 +859,11 @@ def main():
                     help="search: sims/s on fixed positions (the headline); selfplay: games/hour; "
                          "dataset: training samples/s of the dataset build (SURVEY 8f row 2)")
     ap.add_argument("--records", type=int, default=1 << 20, help="dataset mode: replay records per GPU")
+    ap.add_argument("--selfplay-plies", type=int, default=80,
+                    help="search mode: plies of the steady-state self-play window that gives games/hour (0 = skip)")
+    ap.add_argument("--selfplay-warm", type=int, default=160,
+                    help="search mode: cheap 8-simulation plies that spread the games over all ages before the window")
+    ap.add_argument("--s400-steps", type=int, default=2, help="search mode: extra steps at the code preset S=400 (0 = skip)")
     ap.add_argument("--min-games", type=int, default=4096, help="selfplay mode: games to finish per rank")
     ap.add_argument("--max-plies", type=int, default=2000)
     ap.add_argument("--eval-games", type=int, default=64, help="iteration mode: evaluation arena games")

@@ -80,6 +80,11 @@ typedef struct {
                                 independent of the GPU count) */
     int32_t eval_nodes;      /* 1: run the policy-value net for every created non-terminal node, as
                                 the reference does (ai_agent.py:522-523); 0 skips it (diagnostic) */
+    double time_limit_s;     /* AlphaZeroGomokuAI.time_limit (ai_agent.py:183-189): the search stops starting new
+                                simulations once this many wall-clock seconds have passed since the call began.
+                                The reference looks at the clock before every simulation; here the host looks every
+                                4 waves (all G trees advance in lock-step, so they all stop at the same simulation
+                                count).  <= 0 or infinite = no limit (no host synchronisation inside the search). */
 } gz_search_params;
 
 typedef struct {
@@ -90,6 +95,8 @@ typedef struct {
     int64_t rollout_steps;   /* _select_offensive_move calls executed */
     int64_t terminal_leaves; /* simulations whose leaf was already game_over */
     int64_t kernel_launches; /* engine kernels launched since gz_create / last reset */
+    int64_t last_search_simulations; /* simulations per tree of the last gz_search (< num_simulations when
+                                        time_limit_s cut it short) */
 } gz_counters;
 
 /* ---- life cycle --------------------------------------------------------------------------- */
@@ -200,6 +207,14 @@ int gz_search_host(gz_handle h, const uint8_t *h_cells, const uint8_t *h_to_move
 int gz_get_tree(gz_handle h, int32_t g, int32_t cap, int32_t *h_parent, int32_t *h_move,
                 int32_t *h_visits, double *h_value, int32_t *n_nodes);
 
+/* MCTSNode.prior_prob of node `node` (creation order, 0 = root) of game g after gz_search on a handle created with
+ * store_priors = 1 (ai_agent.py:522-523, _get_prior_probability :564-582: GomokuModel.predict's softmax gathered
+ * over the node's valid moves and renormalised).  h_prior f32[225] indexed by raster cell, 0 where the cell is
+ * occupied (the reference keeps the E values of the empty cells in raster order: compress to compare);
+ * *h_value receives the value-head output of the same forward (computed and discarded by the reference,
+ * ai_agent.py:570).  Terminal nodes have no prior (ai_agent.py:522): GZ_ERR_STATE.  Either output may be NULL. */
+int gz_get_priors(gz_handle h, int32_t g, int32_t node, float *h_prior, float *h_value);
+
 /* ---- self-play (training.py:141-218 play_one_game, :77-97 SimpleReplay) ---------------------------------- */
 /* G games are played concurrently on the device, one ply of every game per gz_selfplay_step: the
  * position is searched (gz_search with ai_player = the side to move, as play_one_game alternates
@@ -235,6 +250,10 @@ int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double 
                       int64_t replay_capacity, void *stream);
 /* One ply of every game. */
 int gz_selfplay_step(gz_handle h, void *stream);
+/* `ai.params["num_simulations"] = n` between plies of a running self-play session (the reference re-reads params at
+ * every get_move, ai_agent.py:181; training.py:240 mutates them): the following steps search with n simulations.
+ * bench.py uses it to spread the games over all ages with cheap plies before it times full-budget ones. */
+int gz_selfplay_set_simulations(gz_handle h, int32_t num_simulations);
 /* Moves up to `cap` finished-game records to d_out (device) and frees their space; *h_n = count. */
 int gz_selfplay_drain(gz_handle h, gz_replay_record *d_out, int64_t cap, int64_t *h_n, void *stream);
 /* Current boards of the G games (device, for inspection) and the counters. */
@@ -313,6 +332,11 @@ int gz_set_profiling(gz_handle h, int32_t on);
  * 1 = every kernel on the caller's stream: the setting stage times are meaningful under). */
 int gz_set_lanes(gz_handle h, int32_t lanes);
 int gz_get_stage_times(gz_handle h, double *h_ms /*[GZ_N_STAGES]*/, int64_t *h_launches /*[GZ_N_STAGES]*/);
+/* Batches of at most 256 games are launch-bound (about 50 kernels per wave with microseconds of work each; the
+ * get_move call of one interactive game is G = 1): gz_search runs wave 0 eagerly, captures one wave into a CUDA graph
+ * whose kernels read the simulation index from device memory, and replays it for the other simulations.  Results are
+ * identical either way; on = 0 disables the graph path (stage profiling disables it too). */
+int gz_set_graph(gz_handle h, int32_t on);
 
 /* ---- counters ---------------------------------------------------------------------------------- */
 int gz_get_counters(gz_handle h, gz_counters *out);

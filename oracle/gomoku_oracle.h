@@ -73,6 +73,12 @@ typedef struct {
     int64_t n_planner_steps;
     int64_t n_rollout_steps;
     int64_t n_terminal_leaves;
+    /* Diagnostics of the planner's blended pick (bg_planner.py:256-264), for the near-tie accounting of
+     * the parity tests: over every pick whose argmax was returned (no explore override) the smallest
+     * difference between the best and the second-best composed score, and where it happened. */
+    double min_gap;          /* +inf when no such pick happened */
+    int32_t min_gap_sim, min_gap_step;
+    int64_t n_argmax_picks;
 } gzo_search_stats;
 
 /* ---- rules ---- */
@@ -97,6 +103,15 @@ void gzo_planner_scores(const gzo_board *b, int ai_player, double *scores225);
 int gzo_planner_topk(const gzo_board *b, int ai_player, int k, int32_t *topk);
 int gzo_planner_move(const gzo_board *b, const gzo_params *p, const gzo_weights *w, gzo_rng *rng,
                      int step, int32_t *topk_out, double *composed_out);
+/* same, also recording the near-tie diagnostics into `stats` (may be NULL) */
+int gzo_planner_move_stats(const gzo_board *b, const gzo_params *p, const gzo_weights *w, gzo_rng *rng,
+                           int step, int32_t *topk_out, double *composed_out, gzo_search_stats *stats);
+
+/* Optional memo of the planner networks' outputs keyed by the board (GraphNet softmax + DQN q are pure
+ * functions of the position): n_entries > 0 allocates a direct-mapped table of that many boards, 0 frees it.
+ * Only the fixture generator uses it (1e5 playouts per position share their first planner steps); results
+ * are bit-identical with and without it.  Process-global, not thread-safe. */
+void gzo_set_planner_cache(int n_entries);
 
 /* ---- networks (plain fp32 loops) ---- */
 int64_t gzo_pv_param_count(void);

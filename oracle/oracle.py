@@ -38,7 +38,8 @@ class Params(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("best_move", C.c_int32), ("n_pv_evals", C.c_int64),
                 ("n_planner_steps", C.c_int64), ("n_rollout_steps", C.c_int64),
-                ("n_terminal_leaves", C.c_int64)]
+                ("n_terminal_leaves", C.c_int64), ("min_gap", C.c_double), ("min_gap_sim", C.c_int32),
+                ("min_gap_step", C.c_int32), ("n_argmax_picks", C.c_int64)]
 
 
 PLANNER_PRESETS = {"easy": (8, 0.5, 0.2), "medium": (12, 0.65, 0.1), "hard": (16, 0.75, 0.05)}
@@ -155,6 +156,7 @@ class Oracle:
     def simulate(self, b, p, rng=None):
         fb = Board()
         st = Stats()
+        st.min_gap = float("inf")
         v = self.L.gzo_simulate(C.byref(b), C.byref(p), C.byref(self.w),
                                 C.byref(rng) if rng is not None else None, C.byref(fb), C.byref(st))
         return v, fb, st

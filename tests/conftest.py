@@ -34,6 +34,41 @@ def golden(name):
     return np.load(os.path.join(GOLDEN, name + ".npz"))
 
 
+def report(name, payload):
+    """Measured counts a test wants on record (flip counts, error maxima): gpurun_out/test_reports/<name>.json comes
+    back from the GPU box with the run; the summaries quoted in DESIGN.md / profiles/ are copied from there."""
+    import json
+    d = os.path.join(ROOT, "gpurun_out", "test_reports")
+    try:
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, name + ".json"), "w") as f:
+            json.dump(payload, f, indent=1, default=lambda o: o.tolist() if hasattr(o, "tolist") else str(o))
+    except OSError:
+        pass
+
+
+def host_board(cells, to_move=None, game_over=False, winner=None):
+    """A drop-in GomokuBoard holding `cells` (uint8[225]); the history order is arbitrary (only its length and the
+    stones are read by the hot path)."""
+    from gomoku_board import GomokuBoard
+    b = GomokuBoard()
+    c = np.asarray(cells).reshape(15, 15)
+    b.board = c.astype(int)
+    blk = [(int(r), int(q), 1) for r, q in zip(*np.nonzero(c == 1))]
+    wht = [(int(r), int(q), 2) for r, q in zip(*np.nonzero(c == 2))]
+    hist = []
+    for i in range(max(len(blk), len(wht))):
+        if i < len(blk):
+            hist.append(blk[i])
+        if i < len(wht):
+            hist.append(wht[i])
+    b.move_history = hist
+    b.current_player = int(to_move) if to_move is not None else 1 + len(hist) % 2
+    b.game_over = bool(game_over)
+    b.winner = None if not winner else int(winner)
+    return b
+
+
 @pytest.fixture(scope="session")
 def weights():
     from weights import make_state_dict

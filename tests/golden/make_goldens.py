@@ -19,6 +19,8 @@ Parts (each -> tests/golden/<part>.npz):
   mctsb     DET-B playouts and searches (planner_steps>0)
   stoch     outcome frequencies of real-RNG playouts (Mersenne Twister)
   dataset   SimpleReplay -> GomokuSelfPlayDataset with the 8-fold augmentation   training.py:38-134
+  dropin    the class surface: get_move (book + search, README presets), predict, evaluate_position, prior_prob,
+            BGPlannerAI through AIFactory with the real RNG stream, a checkpoint (-> dropin.npz, ref_checkpoint.pth)
 """
 import argparse
 import os
@@ -770,9 +772,213 @@ def part_update(pool, outdir):
     print("update: train", tl, "val", vl)
 
 
+# ----------------------------------------------------------------------------- part: dropin
+# The reference's CLASS surface, run unmodified: AlphaZeroGomokuAI.get_move (book and search, README
+# presets through the `ai.params[...] = ` idiom of training.py:240), GomokuModel.predict on both input forms,
+# evaluate_position, MCTSNode.prior_prob, BGPlannerAI.get_move with the real Mersenne-Twister stream, and a
+# checkpoint written by GomokuModel.save_model.  The drop-in classes are tested against these on the GPU box.
+WEIGHT_SEED_B = 4321      # a second policy-value model, for the `ai.model = other` re-pack test
+
+
+def _getmove_task(args):
+    seq, player, difficulty, sims, c_puct, planner_steps = args
+    b = board_from_moves(seq)
+    det_patch()
+    ai = ai_agent.AlphaZeroGomokuAI(player, difficulty, device="cpu", beta=0.2, planner_steps=planner_steps,
+                                    time_limit=float("inf"))
+    load_weights(ai.model.model, "pv")
+    load_weights(ai.bg_planner.graph_net, "graphnet")
+    load_weights(ai.bg_planner.opp_dqn, "dqn")
+    ai.params["num_simulations"] = int(sims)     # the reference's own idiom (training.py:240,246)
+    ai.params["c_puct"] = float(c_puct)
+    nodes = []
+    orig_init = ai_agent.MCTSNode.__init__
+
+    def spy_init(self, *a, **k):
+        nodes.append(self)
+        orig_init(self, *a, **k)
+    ai_agent.MCTSNode.__init__ = spy_init
+    t0 = time.time()
+    before = cells_of(b).copy()
+    try:
+        mv = ai.get_move(b)
+    finally:
+        ai_agent.MCTSNode.__init__ = orig_init
+        det_unpatch()
+    assert np.array_equal(before, cells_of(b))           # get_move never mutates the caller's board
+    cv = np.zeros(225, np.int32); cx = np.zeros(225, np.float64)
+    for n in nodes:
+        if n.parent is nodes[0]:
+            cv[n.move[0] * 15 + n.move[1]] = n.visits
+            cx[n.move[0] * 15 + n.move[1]] = n.value
+    return dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(), player=player,
+                difficulty=difficulty, sims=sims, c_puct=c_puct, planner_steps=planner_steps,
+                move=mv[0] * 15 + mv[1], child_visits=cv, child_value=cx, n_nodes=len(nodes),
+                games_played=ai.games_played, seconds=time.time() - t0)
+
+
+def _book_records():
+    """get_move below six stones (ai_agent.py:138-166): the candidate list handed to random.choice and the DET move."""
+    ai = ai_agent.AlphaZeroGomokuAI(1, "easy", device="cpu", planner_steps=0, time_limit=float("inf"))
+    seqs = [[]]
+    b = GomokuBoard()
+    det_patch()
+    for _ in range(5):                                   # the reference's own DET opening line
+        mv = ai.get_move(b)
+        b.make_move(*mv)
+        seqs.append(list(seqs[-1]) + [mv[0] * 15 + mv[1]])
+    det_unpatch()
+    seqs += [[0], [7 * 15 + 7, 0], [6 * 15 + 6, 8 * 15 + 8, 7 * 15 + 6], [0, 14, 210, 224, 100],
+             [6 * 15 + 6, 6 * 15 + 7, 6 * 15 + 8, 7 * 15 + 6, 7 * 15 + 8]]
+    recs = []
+    for seq in seqs:
+        b = board_from_moves(seq)
+        seen = []
+
+        def rec_choice(s):
+            seen.append(list(s))
+            return s[0]
+        random.choice = rec_choice
+        random.random = lambda: 1.0
+        mv = ai.get_move(b)
+        det_unpatch()
+        cand = np.zeros(225, np.uint8)
+        for (r, c) in (seen[0] if seen else []):
+            cand[r * 15 + c] = 1
+        recs.append(dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(),
+                         move=mv[0] * 15 + mv[1], cand=cand, from_choice=int(bool(seen))))
+    return recs
+
+
+def _planner_stream_task(args):
+    seq, player, difficulty, seed, calls = args
+    b = board_from_moves(seq)
+    det_unpatch()
+    pl = ai_agent.AIFactory.create_ai("bg_planner", player, difficulty, device="cpu")
+    assert type(pl) is bg_planner.BGPlannerAI
+    load_weights(pl.graph_net, "graphnet")
+    load_weights(pl.opp_dqn, "dqn")
+    random.seed(seed)
+    moves = []
+    for _ in range(calls):                                # real Mersenne-Twister stream: one random.random() per
+        mv = pl.get_move(b)                               # call, random.choice(top_moves) when it explores
+        moves.append(mv[0] * 15 + mv[1])
+    return dict(cells=cells_of(b), to_move=b.current_player, move_count=b.get_move_count(), player=player,
+                difficulty=difficulty, seed=seed, moves=np.array(moves, np.int32))
+
+
+def part_dropin(pool, outdir):
+    import importlib.util
+    import shutil
+    pos, tags = load_positions(outdir)
+    live = [(p, t) for p, t in zip(pos, tags) if not board_from_moves(p).game_over]
+    dense = [p for p, t in live if t == "dense"]
+    by_len = lambda lo, hi: [p for p in dense if lo <= len(p) <= hi]   # noqa: E731
+    mid = [p for p, t in live if t in ("cluster", "centre") and 90 <= len(p) <= 151]
+    # ---- get_move through the search: README presets (BASELINE configs 1-3) set through ai.params
+    tasks = []
+    for i, p in enumerate(by_len(170, 180)[:3]):
+        tasks.append((p, 1 + len(p) % 2, "easy", 50, 1.2, 0))
+    for i, p in enumerate(by_len(180, 195)[:3]):
+        tasks.append((p, 1 + len(p) % 2, "medium", 100, 1.6, 0))
+    for i, p in enumerate(by_len(190, 198)[:4]):
+        tasks.append((p, 1 + len(p) % 2, "hard", 200, 1.8, 0))
+    for i, p in enumerate(by_len(195, 198)[:3]):
+        tasks.append((p, 1 + len(p) % 2, "hard", 200, 1.8, 5))     # the ctor default planner_steps
+    tasks.append((by_len(190, 194)[0], 1 + len(by_len(190, 194)[0]) % 2, "easy", 50, 1.2, 2))
+    tasks.append((by_len(190, 194)[1], 2 - len(by_len(190, 194)[1]) % 2, "medium", 100, 1.6, 3))   # AI colour != mover
+    tasks.append((mid[0], 1 + len(mid[0]) % 2, "easy", 20, 1.2, 0))
+    tasks.append((mid[-1], 1 + len(mid[-1]) % 2, "hard", 30, 1.8, 0))
+    tasks.append((by_len(196, 199)[-1], 1 + len(by_len(196, 199)[-1]) % 2, "hard", 400, 1.8, 0))    # code preset S=400
+    res_search = pool.map_async(_getmove_task, tasks, chunksize=1)
+    # ---- BGPlannerAI through the factory, real RNG stream
+    ptasks = []
+    for i, p in enumerate([q for q, t in live if 6 <= len(q) <= 60][::5][:6] + by_len(150, 190)[:2]):
+        ptasks.append((p, 1 + (i % 2), ("easy", "medium", "hard")[i % 3], 600 + i, 12))
+    res_planner = pool.map_async(_planner_stream_task, ptasks, chunksize=1)
+
+    out = {}
+    book = _book_records()
+    for k in book[0]:
+        out["book_" + k] = np.stack([np.asarray(r[k]) for r in book])
+
+    # ---- predict (both input forms), evaluate_position, prior_prob: models A (seed 1234) and B (seed 4321)
+    sel = [p for p, t in live][::7][:10]
+    finished = [p for p in pos if board_from_moves(p).game_over][:3]
+    rng = np.random.default_rng(11)
+    draw = dense_pattern_moves(rng, 200)
+    assert board_from_moves(draw).game_over and board_from_moves(draw).winner is None
+    ev_boards = sel[:4] + finished + [draw]
+    for tag, wseed in (("a", WEIGHT_SEED), ("b", WEIGHT_SEED_B)):
+        gm = neural_network.GomokuModel(device="cpu")
+        sd = make_state_dict("pv", wseed)
+        gm.model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}, strict=True)
+        gm.model.eval()
+        pol2, val2, pol3, val3, prior = [], [], [], [], []
+        for p in sel:
+            b = board_from_moves(p)
+            a, v = gm.predict(b.get_board_state())                 # (15,15) ints
+            c, w = gm.predict(b.get_board_tensor())                # (3,15,15) planes
+            pol2.append(a); val2.append(v); pol3.append(c); val3.append(w)
+            node = ai_agent.MCTSNode(b, None, None, gm, {"c_puct": 1.0})
+            pr = np.zeros(225, np.float64)
+            for (r, c2), x in zip(b.get_valid_moves(), node.prior_prob):
+                pr[r * 15 + c2] = x
+            prior.append(pr)
+        out["pred_policy2d_" + tag] = np.stack(pol2).astype(np.float32)
+        out["pred_value2d_" + tag] = np.array(val2, np.float64)
+        out["pred_policy3d_" + tag] = np.stack(pol3).astype(np.float32)
+        out["pred_value3d_" + tag] = np.array(val3, np.float64)
+        out["prior_" + tag] = np.stack(prior)
+        ev = []
+        for player in (1, 2):
+            ai = ai_agent.AlphaZeroGomokuAI(player, "easy", device="cpu", planner_steps=0)
+            ai.model = gm                                          # training.py:247-248 idiom
+            ev.append([ai.evaluate_position(board_from_moves(p)) for p in ev_boards])
+        out["evalpos_" + tag] = np.array(ev, np.float64)
+        if tag == "a":
+            ck = os.path.join(_SCRATCH, "ckpt", "ref_checkpoint.pth")
+            gm.save_model(ck)                                      # neural_network.py:292-306
+            shutil.copy(ck, os.path.join(outdir, "ref_checkpoint.pth"))
+            # and the other direction: a checkpoint written by the drop-in wrapper, loaded by the reference
+            pkg = os.path.join(os.path.dirname(os.path.dirname(HERE)), "alphazero-gomoku_b200")
+            sys.path.insert(0, pkg)
+            spec = importlib.util.spec_from_file_location("dropin_neural_network", os.path.join(pkg, "neural_network.py"))
+            dnn = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(dnn)
+            sys.path.remove(pkg)
+            dm = dnn.GomokuModel(device="cpu")
+            dm.model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}, strict=True)
+            dck = os.path.join(_SCRATCH, "ckpt", "dropin_checkpoint.pth")
+            dm.save_model(dck)
+            back = neural_network.GomokuModel(model_path=dck, device="cpu")
+            b0 = board_from_moves(sel[0])
+            pa, va = back.predict(b0.get_board_state())
+            out["ref_loads_dropin_checkpoint"] = np.array(
+                [float(np.max(np.abs(pa - pol2[0]))), abs(va - val2[0])], np.float64)
+            assert out["ref_loads_dropin_checkpoint"].max() == 0.0
+    out["pred_cells"] = np.stack([cells_of(board_from_moves(p)) for p in sel])
+    eb = [board_from_moves(p) for p in ev_boards]
+    out["evalpos_cells"] = np.stack([cells_of(b) for b in eb])
+    out["evalpos_to_move"] = np.array([b.current_player for b in eb], np.uint8)
+    out["evalpos_move_count"] = np.array([b.get_move_count() for b in eb], np.int32)
+    out["evalpos_game_over"] = np.array([int(b.game_over) for b in eb], np.uint8)
+    out["evalpos_winner"] = np.array([0 if b.winner is None else b.winner for b in eb], np.uint8)
+
+    recs = res_planner.get()
+    for k in recs[0]:
+        out["planner_" + k] = np.stack([np.asarray(r[k]) for r in recs])
+    recs = res_search.get()
+    for k in recs[0]:
+        out["search_" + k] = np.stack([np.asarray(r[k]) for r in recs])
+    np.savez_compressed(os.path.join(outdir, "dropin.npz"), **out)
+    print("dropin: %d book, %d search (%.0f cpu-s), %d planner streams" %
+          (len(book), len(tasks), sum(r["seconds"] for r in recs), len(ptasks)))
+
+
 PARTS = dict(positions=part_positions, boards=part_boards, tiers=part_tiers, rollout=part_rollout,
              mcts=part_mcts, planner=part_planner, nets=part_nets, mctsb=part_mctsb, stoch=part_stoch,
-             dataset=part_dataset, arena=part_arena, update=part_update)
+             dataset=part_dataset, arena=part_arena, update=part_update, dropin=part_dropin)
 
 
 def main():

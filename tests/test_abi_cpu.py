@@ -33,7 +33,7 @@ def test_exports_match_header(lib):
 def test_struct_sizes_and_counts(lib):
     import engine
     import oracle as orc
-    assert C.sizeof(engine.GzSearchParams) == 64 and C.sizeof(engine.GzConfig) == 24
+    assert C.sizeof(engine.GzSearchParams) == 72 and C.sizeof(engine.GzConfig) == 24
     assert lib.gz_pv_param_count() == orc.lib().gzo_pv_param_count() == 711591 + 5 * 256
     assert lib.gz_graphnet_param_count() == 267749 and lib.gz_dqn_param_count() == 296673
 
