@@ -22,16 +22,20 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, out=None, extra_flags=()):
+    """out / extra_flags: an instrumented variant next to the product library (e.g. scratch/gn_timing.py builds
+    libgomoku_b200_timing.so with -DGZ_GN_TIMING); the product build takes neither."""
+    so = out or SO
+    if out is None and not force and not needs_build():
         return SO
     objs = []
     procs = []
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    bdir = os.path.join(HERE, "build" if out is None else "build_" + os.path.basename(out).split(".")[0])
+    os.makedirs(bdir, exist_ok=True)
     for src in SOURCES:
-        obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
+        obj = os.path.join(bdir, src.replace(".cu", ".o"))
         objs.append(obj)
-        cmd = ["nvcc"] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+        cmd = ["nvcc"] + FLAGS + list(extra_flags) + (["-Xptxas", "-v"] if verbose else []) + \
               ["-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     for src, p in procs:
@@ -40,8 +44,8 @@ def build(force=False, verbose=False):
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError("nvcc failed on " + src)
-    subprocess.check_call(["nvcc", "-shared", "-cudart", "static", "-o", SO] + objs)
-    return SO
+    subprocess.check_call(["nvcc", "-shared", "-cudart", "static", "-o", so] + objs)
+    return so
 
 
 if __name__ == "__main__":

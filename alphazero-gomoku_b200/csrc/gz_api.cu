@@ -875,6 +875,7 @@ static int sp_begin(gz_handle h, int32_t G, const gz_search_params *p, double ex
     e->sp_cfg.id_stride = arena ? (uint32_t)ordinal_stride : 1u << 20;
     e->sp_cfg.arena = arena;
     e->sp_cfg.games_total = games_total;
+    e->sp_cfg.n_slots = G;
     e->sp_cfg.sims_a = p->num_simulations;
     e->sp_cfg.sims_b = sims_b > 0 ? sims_b : p->num_simulations;
     if (arena && e->sp_cfg.sims_b > e->cfg.max_simulations)
@@ -892,8 +893,9 @@ static int sp_begin(gz_handle h, int32_t G, const gz_search_params *p, double ex
 }
 
 extern "C" int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration,
-                                 int64_t replay_capacity, void *stream) {
-    return sp_begin(h, G, p, exploration, replay_capacity, 0, 0, 0, 0, stream);
+                                 int64_t replay_capacity, int64_t games_total, void *stream) {
+    if (games_total < 0) return fail(GZ_ERR_ARG, "gz_selfplay_begin: games_total must be >= 0");
+    return sp_begin(h, G, p, exploration, replay_capacity, 0, 0, games_total, 0, stream);
 }
 
 extern "C" int gz_arena_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration, int32_t opponent,

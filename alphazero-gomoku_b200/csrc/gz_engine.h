@@ -136,7 +136,8 @@ struct SelfPlayCfg {
     // evaluation arena (training.py:221-270): 0 = plain self-play; GZ_ARENA_ENGINE / GZ_ARENA_RANDOM: side A's colour
     // alternates with the game ordinal (= game id), games with ordinal >= games_total are played but not counted
     int32_t arena;
-    long long games_total;
+    int32_t n_slots;             // G of the session
+    long long games_total;       // self-play: 0 = open-ended, else games with ordinal generation * G + slot < this count
     int32_t sims_a, sims_b;      // arena: simulations per search of side A / side B (evaluate_model overrides only B's)
     double exploration;
 };

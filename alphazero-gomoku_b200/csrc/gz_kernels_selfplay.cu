@@ -56,8 +56,13 @@ __device__ __forceinline__ int sp_book_bit(const BB &empty, int ply, const SelfP
 
 // side A's colour in the arena: black in even game ordinals (training.py:232,237,266)
 __device__ __forceinline__ int sp_side_a(const SelfPlayCfg &c, uint32_t game_id) { return (game_id & 1u) ? 2 : 1; }
+// Which games are counted and recorded is fixed by their START ordinal, never by when they finish.  Arena: the
+// ordinal is the game id.  Self-play: id = id_base + slot + generation * 2^20, ordinal = generation * G + slot.
 __device__ __forceinline__ bool sp_counted(const SelfPlayCfg &c, uint32_t game_id) {
-    return c.arena == 0 || c.games_total <= 0 || (long long)game_id < c.games_total;
+    if (c.games_total <= 0) return true;
+    if (c.arena != 0) return (long long)game_id < c.games_total;
+    const uint32_t rel = game_id - c.id_base;
+    return (long long)(rel >> 20) * c.n_slots + (long long)(rel & 0xFFFFFu) < c.games_total;
 }
 
 // lane 0: empty board, then every ply that needs no search: the six opening-book plies

@@ -18,6 +18,7 @@
 //   warp 1    single-thread tcgen05.mma issuer; accumulators double buffered in TMEM
 //   warps 2-5 epilogue: tcgen05.ld, bias (+ residual) + ReLU, zero the padding positions, pack to
 //             bf16, 16-byte coalesced stores
+#include <cstdio>
 #include <cstdlib>
 #include "gz_engine.h"
 #include "gz_tcgen05.cuh"
@@ -377,6 +378,12 @@ k_planes_to_nchw(const uint8_t *__restrict__ planes, int C, const uint8_t *__res
 // epilogue:  MMA3(0) MMA3(1) MMA1(0) MMA3(2) MMA1(1) ...
 //   warp 0     slab producer (bulk copies)          warps 1, 10  tcgen05.mma issuers (M half 0 / 1)
 //   warps 2-9  epilogues: quadrant = warp & 3, M half = (warp - 2) >> 2
+// -DGZ_GN_TIMING: block 0 prints where its producer / issuer / epilogue warps spend their cycles (scratch/gn_timing.py)
+#ifdef GZ_GN_TIMING
+#define GN_T(...) __VA_ARGS__
+#else
+#define GN_T(...)
+#endif
 struct GnBlockCfg {
     static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
     static constexpr int MID_BYTES = 8 * 256 * 16;
@@ -440,15 +447,19 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
             ptx::mbar_expect_tx(w_full, C::W3_BYTES + C::W1_BYTES);
             for (int t = 0; t < 9; ++t) ptx::bulk_g2s(sw3 + t * 8192, w3 + t * 8192, 8192, w_full);
             ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
+            GN_T(long long w_ae = 0;)
             for (int it = 0; it < n_it; ++it) {
                 const int b = blockIdx.x + it * gridDim.x, ab = it & 1;
+                GN_T(long long t0 = clock64();)
                 ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+                GN_T(w_ae += clock64() - t0;)
                 ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
                 const uint8_t *src = in_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes - 16;
                 for (int cg = 0; cg < 8; ++cg)
                     ptx::bulk_g2s(slab + ab * C::SLAB_BYTES + cg * C::SLAB_ROWS * 16,
                                   src + (size_t)cg * kPlaneBytes, C::SLAB_ROWS * 16, &a_full[ab]);
             }
+            GN_T(if (blockIdx.x == 0) printf("gn producer: wait a_empty %lld per board\n", w_ae / (n_it > 0 ? n_it : 1));)
         }
     } else if (warp == 1 || warp == 10) {
         // Two issuer warps, one per M half of the board (rows 0-127 / 128-255, separate accumulators): while one
@@ -457,14 +468,19 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
         {   // whole warp; one elected lane issues (gz_tcgen05.cuh)
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 64);
             constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = 64 * 16;
+            GN_T(long long tk0 = clock64(); long long w_d1e = 0, w_af = 0, t_i3 = 0, w_mf = 0, w_d2e = 0, t_i1 = 0;)
             ptx::mbar_wait(w_full, 0);
+            GN_T(const long long w_w = clock64() - tk0;)
             const uint32_t w3_addr = ptx::smem_u32(sw3), w1_addr = ptx::smem_u32(sw1);
             for (int it = 0; it <= n_it; ++it) {
                 if (it < n_it) {
                     const int ab = it & 1;
                     const uint32_t par = (it >> 1) & 1;
+                    GN_T(long long t0 = clock64();)
                     ptx::mbar_wait(&d1_empty[ab], par ^ 1);
+                    GN_T(long long t1 = clock64(); w_d1e += t1 - t0;)
                     ptx::mbar_wait(&a_full[ab], par);
+                    GN_T(long long t2 = clock64(); w_af += t2 - t1;)
                     ptx::tc_fence_after();
                     // Descriptors = one base per operand + compile-time constants in the 16-byte address field:
                     // at N = 64 a UMMA lasts 48 cycles and anything more per instruction shows (the loop is fully
@@ -485,12 +501,16 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                     }
                     ptx::umma_commit_elect(&a_empty[ab]);
                     ptx::umma_commit_elect(&d1_full[ab]);
+                    GN_T(t_i3 += clock64() - t2;)
                 }
                 if (it > 0) {
                     const int j = it - 1, jb = j & 1;
                     const uint32_t par = (j >> 1) & 1;
+                    GN_T(long long t0 = clock64();)
                     ptx::mbar_wait(&mid_full[jb], par);
+                    GN_T(long long t1 = clock64(); w_mf += t1 - t0;)
                     ptx::mbar_wait(&d2_empty[jb], par ^ 1);
+                    GN_T(long long t2 = clock64(); w_d2e += t2 - t1;)
                     ptx::tc_fence_after();
                     // A = the 3x3 result packed to bf16 in place in its accumulator columns (epilogue 1): TS form
                     const uint64_t dw0 = ptx::make_desc(w1_addr, LBO_B, 128);
@@ -502,8 +522,12 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                                                 dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
                     ptx::umma_commit_elect(&mid_empty[jb]);
                     ptx::umma_commit_elect(&d2_full[jb]);
+                    GN_T(t_i1 += clock64() - t2;)
                 }
             }
+            GN_T(if (blockIdx.x == 0 && lane == 0 && n_it > 0)
+                     printf("gn issuer h=%d: %d boards, total %lld | per board: wait d1_empty %lld, a_full %lld, issue3x3 %lld, wait mid_full %lld, d2_empty %lld, issue1x1 %lld | weights %lld\n",
+                            h, n_it, clock64() - tk0, w_d1e / n_it, w_af / n_it, t_i3 / n_it, w_mf / n_it, w_d2e / n_it, t_i1 / n_it, w_w);)
         }
     } else {
         const int q = warp & 3, h = (warp - 2) >> 2;
@@ -511,12 +535,16 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
         const int pos = 16 + row;
         const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
         const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 64;
+        GN_T(long long w_d1f = 0, w_me = 0, t_e1 = 0, w_d2f = 0, t_e2 = 0;)
         for (int it = 0; it <= n_it; ++it) {
             if (it < n_it) {
                 const int ab = it & 1;
                 const uint32_t par = (it >> 1) & 1;
+                GN_T(long long t0 = clock64();)
                 ptx::mbar_wait(&d1_full[ab], par);
+                GN_T(long long t1 = clock64(); w_d1f += t1 - t0;)
                 ptx::mbar_wait(&mid_empty[ab], par ^ 1);
+                GN_T(long long t2 = clock64(); w_me += t2 - t1;)
                 ptx::tc_fence_after();
                 // bias + ReLU + bf16 pack, written back IN PLACE over the accumulator's first 32 columns (the write
                 // cursor c0/2 never passes the read cursor c0): the 1x1 reads it as its A operand from TMEM
@@ -535,11 +563,14 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
+                GN_T(t_e1 += clock64() - t2;)
             }
             if (it > 0) {
                 const int j = it - 1, jb = j & 1;
                 const int b = blockIdx.x + j * gridDim.x;
+                GN_T(long long t0 = clock64();)
                 ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
+                GN_T(long long t1 = clock64(); w_d2f += t1 - t0;)
                 ptx::tc_fence_after();
                 if (FINAL) {
                     float p0 = kc.head_b[0], p1 = kc.head_b[1];
@@ -577,8 +608,12 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+                GN_T(t_e2 += clock64() - t1;)
             }
         }
+        GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 2 || warp == 9) && n_it > 0)
+                 printf("gn epilogue warp %d: per board: wait d1_full %lld, mid_empty %lld, epi1 %lld, wait d2_full %lld, epi2 %lld\n",
+                        warp, w_d1f / n_it, w_me / n_it, t_e1 / n_it, w_d2f / n_it, t_e2 / n_it);)
     }
     ptx::tc_fence_before();
     __syncthreads();

@@ -299,10 +299,12 @@ class Engine:
         return cv, cval, best
 
     # ---- self-play
-    def selfplay_begin(self, n_games, params, exploration, replay_capacity=0):
+    def selfplay_begin(self, n_games, params, exploration, replay_capacity=0, games_total=0):
+        """games_total = N > 0: exactly the N games with start ordinal generation * n_games + slot < N are counted and
+        recorded (the reference's `for game in range(N)`); 0 = open-ended recycling."""
         self._sp_games = int(n_games)
         self._ck(self.L.gz_selfplay_begin(self.h, int(n_games), C.byref(params), C.c_double(exploration),
-                                          C.c_int64(replay_capacity), self._stream()))
+                                          C.c_int64(replay_capacity), C.c_int64(games_total), self._stream()))
 
     def arena_begin(self, n_games, params, exploration, opponent, games_total, ordinal_stride=None,
                     replay_capacity=0, sims_b=0):

@@ -60,8 +60,15 @@ class AlphaZeroGomokuNet(nn.Module):
 
 def weights_version(module):
     """Cheap change detector: torch bumps `_version` on every in-place update (optimizer steps,
-    load_state_dict), so the engine re-packs weights only when this tuple changes."""
-    return (id(module),) + tuple(int(t._version) for t in module.state_dict(keep_vars=True).values())
+    load_state_dict), so the engine re-packs weights only when this tuple changes.  Updates torch cannot see
+    (parameters written by a CUDA-graph replay) are announced with mark_weights_changed()."""
+    return (id(module), getattr(module, "_gz_generation", 0)) + \
+        tuple(int(t._version) for t in module.state_dict(keep_vars=True).values())
+
+
+def mark_weights_changed(module):
+    """Call after updating a module's parameters behind torch's back (training.GraphedTrainStep replays)."""
+    module._gz_generation = getattr(module, "_gz_generation", 0) + 1
 
 
 def planes_to_cells(board_state):

@@ -52,14 +52,18 @@ class SelfPlay:
     model / planner nets configure every search, exactly as the two AIs sharing one model do in
     training.py:403-408.  rank / world place this GPU's games in the global id space."""
 
-    def __init__(self, ai, n_games, rank=0, world=1, seed=0, replay_capacity=0, lanes=0):
+    def __init__(self, ai, n_games, rank=0, world=1, seed=0, replay_capacity=0, lanes=0, games_total=0):
         self.ai, self.n_games, self.rank, self.world = ai, int(n_games), int(rank), int(world)
         sims = int(ai.params["num_simulations"])
         self.engine = ai._get_engine(self.n_games, sims)
         p = ai._search_params(game_base=self.rank * self.n_games)
         p.seed = (int(seed) * 0x9E3779B97F4A7C15 + 0xB200) & (2 ** 64 - 1)
         self.params = p
-        self.engine.selfplay_begin(self.n_games, p, float(ai.params["exploration"]), replay_capacity)
+        self.games_total = int(games_total)
+        if self.games_total and not replay_capacity:     # every counted game fits: nothing is ever dropped
+            replay_capacity = 200 * self.games_total
+        self.engine.selfplay_begin(self.n_games, p, float(ai.params["exploration"]), replay_capacity,
+                                   self.games_total)
 
     def step(self, n=1):
         for _ in range(n):
@@ -76,17 +80,22 @@ class SelfPlay:
     def drain_device(self):
         return self.engine.selfplay_drain()
 
-    def play_games(self, n_finished, max_steps=100000):
-        """Steps until this rank has finished at least n_finished games; returns their records."""
+    def play_games(self, n_finished=None, max_steps=100000):
+        """Steps until the session's games_total games (or, in an open-ended session, at least n_finished games) are
+        finished; returns their records.  With games_total the recorded games are the FIRST games_total starts, all
+        played to the end, like the reference's `for game in range(N): play_one_game(...)` (training.py:415-420); an
+        open-ended session stopped at a count keeps whichever games finished first (short games over-represented)."""
+        target = self.games_total or int(n_finished)
         out = []
         for _ in range(max_steps):
             self.step()
             st = self.stats()
             if st["records_ready"] > self.n_games * 128:
                 out.append(self.drain())
-            if st["games_finished"] >= n_finished:
+            if st["games_finished"] >= target:
                 break
         out.append(self.drain())
+        assert self.stats()["records_dropped"] == 0, "replay buffer overflow: records were dropped"
         return np.concatenate(out)
 
 

@@ -19,11 +19,11 @@ import torch.nn as nn
 import engine as _engine
 from ai_agent import AlphaZeroGomokuAI
 from gomoku_board import GomokuBoard
-from neural_network import GomokuModel
+from neural_network import GomokuModel, mark_weights_changed
 from selfplay import GomokuSelfPlayDataset, SelfPlay, gather_replay, records_to_samples
 
 __all__ = ["SimpleReplay", "GomokuSelfPlayDataset", "Arena", "play_games", "evaluate_model", "DeviceLoader",
-           "GraphedTrainStep", "train_epoch", "validate_epoch", "run_iteration", "main"]
+           "GraphedTrainStep", "train_epoch", "validate_epoch", "run_iteration", "main", "shard_batches"]
 
 
 class SimpleReplay:
@@ -154,14 +154,58 @@ class DeviceLoader:
             yield self.dataset.batch(idx[i:i + self.batch_size])
 
 
+def shard_batches(indices, global_batch, rank, world):
+    """Data-parallel split of a sample order: global batch b is indices[b*B:(b+1)*B]; rank r trains on its r-th
+    1/world of every global batch, so the mean of the ranks' gradients is the gradient of the global batch's mean loss.
+    A ragged last batch is cut down to a multiple of world (at most world - 1 samples are left out).  Returns this
+    rank's index list and its local batch size."""
+    B = int(global_batch)
+    local = B // world
+    assert local * world == B, "the global batch must be a multiple of the number of ranks"
+    out = []
+    for lo in range(0, len(indices), B):
+        chunk = indices[lo:lo + B]
+        per = len(chunk) // world
+        out.extend(chunk[rank * per:(rank + 1) * per])
+    return out, local
+
+
+def _sync_grads(model, world, group):
+    """One all-reduce of the flattened fp32 gradient (2.8 MB for the policy-value net), averaged over the ranks.
+    Works eagerly and inside a CUDA-graph capture (NCCL collectives are capturable)."""
+    import torch.distributed as dist
+    grads = [p.grad for p in model.model.parameters() if p.grad is not None]
+    flat = torch.cat([g.reshape(-1) for g in grads])
+    dist.all_reduce(flat, group=group)
+    flat.div_(world)
+    off = 0
+    for g in grads:
+        n = g.numel()
+        g.copy_(flat[off:off + n].view_as(g))
+        off += n
+
+
+def _mean_over_ranks(value, count, device, world, group):
+    """Sum of per-batch losses and batch count -> mean over every rank's batches (identical on all ranks)."""
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([float(value), float(count)], dtype=torch.float64, device=device)
+        dist.all_reduce(t, group=group)
+        value, count = t[0].item(), t[1].item()
+    return float(value) / max(1.0, count) if count else 0.0
+
+
 def _losses(model, x, y_policy, y_value):
     policy_logits, value_pred = model.model(x)
     return nn.functional.cross_entropy(policy_logits, y_policy) + nn.functional.mse_loss(value_pred, y_value)
 
 
-def train_epoch(model, loader, optimizer, device, grad_clip=1.0, epoch_index=1, num_epochs=1):
+def train_epoch(model, loader, optimizer, device, grad_clip=1.0, epoch_index=1, num_epochs=1, world=1, group=None):
     """training.py:277-311: CE on the played move + MSE on the outcome, clip_grad_norm_, optimizer.step; returns the
-    mean batch loss.  The per-batch `loss.item()` of the reference (a device sync per batch) becomes a float64
+    mean batch loss.  world > 1: data-parallel -- `loader` holds this rank's share of every global batch
+    (shard_batches), the gradient is averaged over the ranks before clipping (one all-reduce per step), so every rank
+    applies the same update and the weights stay in sync without a broadcast; the returned loss is the mean over all
+    ranks' batches.  The per-batch `loss.item()` of the reference (a device sync per batch) becomes a float64
     accumulator on the device read once per epoch -- the same sum of float32 losses in float64.
 
     When the loader is a DeviceLoader over materialized device tensors and the optimizer was built with
@@ -171,20 +215,22 @@ def train_epoch(model, loader, optimizer, device, grad_clip=1.0, epoch_index=1, 
     if (isinstance(loader, DeviceLoader) and isinstance(loader.dataset, _Materialized)
             and optimizer.defaults.get("capturable") and torch.device(device).type == "cuda"
             and len(loader.indices) >= loader.batch_size):
-        return _train_epoch_graphed(model, loader, optimizer, device, grad_clip)
+        return _train_epoch_graphed(model, loader, optimizer, device, grad_clip, world, group)
     total, batches = None, 0
     for x, y_policy, y_value in loader:
         x, y_policy, y_value = x.to(device), y_policy.to(device), y_value.to(device)
         optimizer.zero_grad()
         loss = _losses(model, x, y_policy, y_value)
         loss.backward()
+        if world > 1:
+            _sync_grads(model, world, group)
         if grad_clip is not None and grad_clip > 0:
             nn.utils.clip_grad_norm_(model.model.parameters(), grad_clip)
         optimizer.step()
         d = loss.detach().double()
         total = d if total is None else total + d
         batches += 1
-    return float(total) / max(1, batches) if batches else 0.0
+    return _mean_over_ranks(total if total is not None else 0.0, batches, device, world, group)
 
 
 class GraphedTrainStep:
@@ -195,8 +241,9 @@ class GraphedTrainStep:
     place afterwards (parameters, BatchNorm buffers, Adam moments and step counters), so the captured run starts from
     exactly the state it was given."""
 
-    def __init__(self, model, optimizer, data, batch_size, grad_clip):
+    def __init__(self, model, optimizer, data, batch_size, grad_clip, world=1, group=None):
         self.model, self.optimizer, self.data, self.grad_clip = model, optimizer, data, grad_clip
+        self.world, self.group = world, group
         dev = data.planes.device
         self.idx = torch.zeros(batch_size, dtype=torch.long, device=dev)
         self.total = torch.zeros((), dtype=torch.float64, device=dev)
@@ -235,6 +282,8 @@ class GraphedTrainStep:
         self.optimizer.zero_grad(set_to_none=True)
         loss = _losses(self.model, x, y, v)
         loss.backward()
+        if self.world > 1:                             # data-parallel: the all-reduce is a node of the graph
+            _sync_grads(self.model, self.world, self.group)
         if self.grad_clip is not None and self.grad_clip > 0:
             nn.utils.clip_grad_norm_(self.model.model.parameters(), self.grad_clip)
         self.optimizer.step()
@@ -245,7 +294,7 @@ class GraphedTrainStep:
         self.graph.replay()
 
 
-def _train_epoch_graphed(model, loader, optimizer, device, grad_clip):
+def _train_epoch_graphed(model, loader, optimizer, device, grad_clip, world=1, group=None):
     idx = list(loader.indices)
     if loader.shuffle:
         loader.rng.shuffle(idx)
@@ -253,7 +302,7 @@ def _train_epoch_graphed(model, loader, optimizer, device, grad_clip):
     data = loader.dataset.d
     perm = torch.as_tensor(idx, dtype=torch.long, device=data.planes.device)
     n_full = len(idx) // B
-    step = GraphedTrainStep(model, optimizer, data, B, grad_clip)
+    step = GraphedTrainStep(model, optimizer, data, B, grad_clip, world, group)
     for i in range(n_full):
         step.run(perm[i * B:(i + 1) * B])
     total, batches = step.total.clone(), n_full
@@ -262,16 +311,20 @@ def _train_epoch_graphed(model, loader, optimizer, device, grad_clip):
         optimizer.zero_grad()
         loss = _losses(model, data.planes[tail], data.move[tail], data.value[tail].reshape(-1, 1))
         loss.backward()
+        if world > 1:
+            _sync_grads(model, world, group)
         if grad_clip is not None and grad_clip > 0:
             nn.utils.clip_grad_norm_(model.model.parameters(), grad_clip)
         optimizer.step()
         total = total + loss.detach().double()
         batches += 1
-    return float(total) / max(1, batches)
+    mark_weights_changed(model.model)                  # graph replays do not bump the tensors' _version
+    return _mean_over_ranks(total, batches, device, world, group)
 
 
-def validate_epoch(model, loader, device, epoch_index=1, num_epochs=1):
-    """training.py:314-337."""
+def validate_epoch(model, loader, device, epoch_index=1, num_epochs=1, world=1, group=None):
+    """training.py:314-337.  world > 1: `loader` is this rank's share of the validation batches; the mean is taken
+    over every rank's batches, so all ranks see the same number (and take the same best-model / early-stop decisions)."""
     model.eval_mode()
     total, batches = None, 0
     with torch.no_grad():
@@ -280,7 +333,7 @@ def validate_epoch(model, loader, device, epoch_index=1, num_epochs=1):
             d = _losses(model, x, y_policy, y_value).double()
             total = d if total is None else total + d
             batches += 1
-    return float(total) / max(1, batches) if batches else 0.0
+    return _mean_over_ranks(total if total is not None else 0.0, batches, device, world, group)
 
 
 # ---------------------------------------------------------------------------------------------- one iteration
@@ -294,14 +347,18 @@ def _sync_time(device):
 def run_iteration(model, optimizer, scheduler, device, games_per_iteration=10, concurrent=None, difficulty="medium",
                   beta=0.2, planner_steps=5, num_simulations=None, c_puct=None, augment_ratio=0.35, train_split=0.9,
                   batch_size=128, epochs=2, grad_clip=0.8, eval_games=6, baseline=None, rank=0, world=1, seed=0,
-                  precision="bf16", reference_exact=True, group=None):
+                  precision="bf16", reference_exact=True, group=None, update=None):
     """One pass of training.py:401-508: self-play -> (all-gather) -> dataset with 8-fold augmentation -> 90/10 split ->
     `epochs` x (train_epoch, validate_epoch) -> scheduler.step -> evaluation games.  Returns the losses, the
     evaluation result and the wall time of every phase (device-synchronised).
 
-    Multi-GPU: every rank plays games_per_iteration / world games, the packed records are all-gathered
-    (the one collective), and every rank then runs the SAME update on the gathered set -- the reference's
-    single-trainer semantics, no gradient exchange; rank 0's weights are broadcast at the end so ranks cannot drift."""
+    Multi-GPU: every rank plays games_per_iteration / world games and the packed records are
+    all-gathered (off the hot path).  update = "dp" (default when world > 1): data-parallel update -- every rank trains
+    on its 1/world of each global batch of `batch_size` samples, one all-reduce of the 2.8 MB gradient per step, the
+    weights stay in sync by construction, BatchNorm running statistics (per-rank batch statistics) are averaged at the
+    end, losses are means over all ranks.  update = "replicated": every rank runs the SAME update on the whole
+    gathered set with the global batch (the reference's single-trainer semantics, training.py:277-337,387-393), then
+    rank 0 broadcasts weights, buffers and the losses it decided on."""
     import torch.distributed as dist
     phases = {}
     t0 = _sync_time(device)
@@ -314,7 +371,10 @@ def run_iteration(model, optimizer, scheduler, device, games_per_iteration=10, c
     ai.model = model
     model.eval_mode()
     mine = -(-int(games_per_iteration) // world)
-    sp = SelfPlay(ai, int(concurrent or min(mine, 4096)), rank=rank, world=world, seed=seed)
+    # exactly `mine` complete games per rank, fixed by start order before any is played (training.py:415-420 plays
+    # N whole games): stopping at the first `mine` finishers would keep the short games and never record a 200-ply draw
+    n_slots = int(concurrent or min(mine, 4096))
+    sp = SelfPlay(ai, min(n_slots, mine), rank=rank, world=world, seed=seed, games_total=mine)
     # records stay on the device: drained as a uint8 tensor, gathered, decoded by gz_dataset_build
     parts = []
     while True:
@@ -324,6 +384,7 @@ def run_iteration(model, optimizer, scheduler, device, games_per_iteration=10, c
             parts.append(sp.drain_device())
         if st["games_finished"] >= mine:
             break
+    assert st["records_dropped"] == 0, "replay buffer overflow: %d records dropped" % st["records_dropped"]
     records = torch.cat(parts, dim=0)
     t1 = _sync_time(device)
     phases["selfplay_s"] = t1 - t0
@@ -337,22 +398,45 @@ def run_iteration(model, optimizer, scheduler, device, games_per_iteration=10, c
     phases["dataset_s"] = t3 - t2
     out = {"games": int(st["games_finished"]), "records": int(records.shape[0]), "samples": len(dataset),
            "selfplay_stats": st}
+    dp = world > 1 and dist.is_initialized() and (update or "dp") == "dp"
+    out["update_mode"] = "dp" if dp else ("replicated" if world > 1 else "single")
     if len(dataset) >= 8:
         idx = list(range(len(dataset)))
         rng.shuffle(idx)
         split = int(len(dataset) * train_split)
-        train_loader = DeviceLoader(_Materialized(dataset), idx[:split], batch_size, shuffle=True, rng=rng)
-        val_loader = DeviceLoader(_Materialized(dataset), idx[split:], batch_size, shuffle=False)
+        data = _Materialized(dataset)
         tl, vl = [], []
-        for ep in range(epochs):
-            tl.append(train_epoch(model, train_loader, optimizer, device, grad_clip, ep + 1, epochs))
-            vl.append(validate_epoch(model, val_loader, device, ep + 1, epochs))
+        if dp:
+            val_idx, local_b = shard_batches(idx[split:], batch_size, rank, world)
+            val_loader = DeviceLoader(data, val_idx, local_b, shuffle=False)
+            train_idx = idx[:split]
+            for ep in range(epochs):
+                rng.shuffle(train_idx)                   # the same order on every rank (shared seed)
+                mine_idx, local_b = shard_batches(train_idx, batch_size, rank, world)
+                loader = DeviceLoader(data, mine_idx, local_b, shuffle=False)
+                tl.append(train_epoch(model, loader, optimizer, device, grad_clip, ep + 1, epochs, world, group))
+                vl.append(validate_epoch(model, val_loader, device, ep + 1, epochs, world, group))
+            with torch.no_grad():                        # BatchNorm running statistics were fed rank-local batches
+                for b in model.model.buffers():
+                    if b.dtype.is_floating_point:
+                        dist.all_reduce(b, group=group)
+                        b.div_(world)
+        else:
+            train_loader = DeviceLoader(data, idx[:split], batch_size, shuffle=True, rng=rng)
+            val_loader = DeviceLoader(data, idx[split:], batch_size, shuffle=False)
+            for ep in range(epochs):
+                tl.append(train_epoch(model, train_loader, optimizer, device, grad_clip, ep + 1, epochs))
+                vl.append(validate_epoch(model, val_loader, device, ep + 1, epochs))
+            if world > 1 and dist.is_initialized():      # rank 0 decides: weights, buffers and the losses it saw
+                for t in list(model.model.parameters()) + list(model.model.buffers()):
+                    dist.broadcast(t.data, src=0, group=group)
+                lt = torch.tensor(tl + vl, dtype=torch.float64, device=device)
+                dist.broadcast(lt, src=0, group=group)
+                tl, vl = lt[:len(tl)].tolist(), lt[len(tl):].tolist()
         if scheduler is not None:
             scheduler.step()
+        model._packed = None                             # graph replays update parameters without bumping _version
         out.update(train_loss=float(np.mean(tl)), val_loss=float(np.mean(vl)))
-        if world > 1 and dist.is_initialized():
-            for t in list(model.model.parameters()) + list(model.model.buffers()):
-                dist.broadcast(t.data, src=0, group=group)
     t4 = _sync_time(device)
     phases["update_s"] = t4 - t3
     if eval_games:

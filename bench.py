@@ -718,6 +718,69 @@ def run_iteration(args):
         dist.destroy_process_group()
 
 
+def run_latency(args):
+    """BASELINE config 1 through the drop-in classes: ONE self-play game, easy preset as the README quotes it (50
+    simulations, c_puct 1.2, set through ai.params like training.py:240), beta 0.2, planner_steps 5, two
+    AlphaZeroGomokuAI objects sharing one GomokuModel (training.py:403-408), G = 1 per get_move call: the interactive
+    call pattern of game_ui.py:178 / training.py:173.  Reports milliseconds per searched move and per game; every
+    get_move includes its host<->device copies.  --games-latency games are played, the first is warm-up."""
+    import random
+    import torch
+    from ai_agent import AlphaZeroGomokuAI
+    from gomoku_board import GomokuBoard
+    from neural_network import GomokuModel
+    torch.manual_seed(1234)
+    random.seed(1234)
+    shared = GomokuModel(device="cuda")
+    ais = {}
+    for player in (1, 2):
+        ai = AlphaZeroGomokuAI(player, "easy", device="cuda", beta=0.2, planner_steps=5, time_limit=float("inf"),
+                               precision=args.precision, seed=99 + player)
+        ai.model = shared
+        ai.params["num_simulations"] = 50
+        ai.params["c_puct"] = 1.2
+        ais[player] = ai
+    sampler = ClockSampler(0)
+    games = []
+    for gi in range(1 + args.games_latency):
+        if gi == 1:
+            sampler.start()
+        b = GomokuBoard()
+        per_move, t_game = [], time.perf_counter()
+        while not b.game_over:
+            ai = ais[b.current_player]
+            searched = b.get_move_count() >= 6
+            t0 = time.perf_counter()
+            mv = ai.get_move(b)
+            dt = time.perf_counter() - t0
+            if mv is None:
+                break
+            if searched:
+                per_move.append(dt * 1e3)
+            b.make_move(*mv)
+        games.append(dict(plies=b.get_move_count(), seconds=time.perf_counter() - t_game, ms=per_move,
+                          winner=b.winner))
+    clocks = sampler.finish()
+    timed = games[1:]
+    ms = sorted(x for g in timed for x in g["ms"])
+    launches = sum(ai._engine.counters()["kernel_launches"] for ai in ais.values() if ai._engine)
+    med = ms[len(ms) // 2]
+    emit(json.dumps({
+        "metric": "get_move_latency_ms", "value": med, "unit": "ms per searched move (median)", "n_gpus": 1,
+        "steps": len(ms), "warmup": 1, "ms_per_step": med, "higher_is_better": False, "scaling": "weak",
+        "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+        "config": {"workload": "BASELINE config 1: easy preset (50 sims, c_puct 1.2, beta 0.2, planner_steps 5, epsilon "
+                               "0.2), one self-play game at a time through AlphaZeroGomokuAI.get_move, G = 1",
+                   "weights": "random init (torch default, seed 1234)"},
+        "clocks": clocks, "mean_ms": sum(ms) / len(ms), "p90_ms": ms[int(0.9 * (len(ms) - 1))], "max_ms": ms[-1],
+        "sims_per_sec_g1": 50.0 / (sum(ms) / len(ms) / 1e3),
+        "games": [dict(plies=g["plies"], seconds=round(g["seconds"], 4), winner=g["winner"]) for g in timed],
+        "seconds_per_game": sum(g["seconds"] for g in timed) / len(timed),
+        "gpu_launches": launches,
+        "reference": "the Python reference needs ~9.5 s per move as shipped (time_limit 5 s: 2 simulations complete) "
+                     "and ~400 s for 50 simulations on an early-game board (BASELINE.md section 2)"}))
+
+
 def synthetic_records(n, seed):
     """n packed replay records (72 B) of random mid-game positions, vectorised: stone k of a random permutation
     of the cells goes to colour k & 1, the record's move is the next cell of the permutation."""
@@ -855,7 +918,7 @@ def main():
                     help="independent game groups advanced on separate CUDA streams (0 = engine default)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "f32"],
                     help="network arithmetic: bf16 tcgen05 (timed mode) or fp32 FFMA (parity mode)")
-    ap.add_argument("--mode", default="search", choices=["search", "selfplay", "dataset", "iteration"],
+    ap.add_argument("--mode", default="search", choices=["search", "selfplay", "dataset", "iteration", "latency"],
                     help="search: sims/s on fixed positions (the headline); selfplay: games/hour; "
                          "dataset: training samples/s of the dataset build (SURVEY 8f row 2)")
     ap.add_argument("--records", type=int, default=1 << 20, help="dataset mode: replay records per GPU")
@@ -864,6 +927,7 @@ def main():
     ap.add_argument("--selfplay-warm", type=int, default=160,
                     help="search mode: cheap 8-simulation plies that spread the games over all ages before the window")
     ap.add_argument("--s400-steps", type=int, default=2, help="search mode: extra steps at the code preset S=400 (0 = skip)")
+    ap.add_argument("--games-latency", type=int, default=3, help="latency mode: timed games (one more is played first)")
     ap.add_argument("--min-games", type=int, default=4096, help="selfplay mode: games to finish per rank")
     ap.add_argument("--max-plies", type=int, default=2000)
     ap.add_argument("--eval-games", type=int, default=64, help="iteration mode: evaluation arena games")
@@ -877,6 +941,8 @@ def main():
         return run_iteration(args)
     if args.mode == "dataset" and args.impl != "reference":
         return run_dataset(args)
+    if args.mode == "latency" and args.impl != "reference":
+        return run_latency(args)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -245,9 +245,14 @@ typedef struct {
 /* Starts G (<= max_games) fresh games.  `p` as for gz_search (num_simulations <= max_simulations);
  * p->seed keys every random choice, p->game_base is the id of this handle's first game (rank * G on a
  * multi-GPU run, so ids and random streams are global).  Replay capacity: replay_capacity records
- * (0 = 256 per game). */
+ * (0 = 256 per game).
+ * games_total = 0: open-ended session, every finished game is counted and recorded (throughput runs).
+ * games_total = N > 0: exactly N complete games, like the reference's `for game in range(N): play_one_game`
+ * (training.py:415-420): the counted games are those with start ordinal generation * G + slot < N (a set fixed
+ * before any game is played, so game length cannot select what is recorded); later games only keep their slot
+ * busy and are neither counted nor recorded.  The session is complete when games_finished == N. */
 int gz_selfplay_begin(gz_handle h, int32_t G, const gz_search_params *p, double exploration,
-                      int64_t replay_capacity, void *stream);
+                      int64_t replay_capacity, int64_t games_total, void *stream);
 /* One ply of every game. */
 int gz_selfplay_step(gz_handle h, void *stream);
 /* `ai.params["num_simulations"] = n` between plies of a running self-play session (the reference re-reads params at

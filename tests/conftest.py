@@ -80,3 +80,29 @@ def weights():
 def oracle(weights):
     import oracle as orc
     return orc.Oracle(**weights)
+
+
+_BLEND_ERR = {}
+
+
+def bf16_blend_error(weights, G=4096):
+    """Largest |composed_bf16 - composed_fp32| of the planner's blended candidate score (bg_planner.py:256-264) over
+    the <= 16 candidates of G workload positions, both measured by the engine; the fp32 side is pinned to the
+    reference within 1e-4 by test_planner_scores_topk_move.  Returns (err, fp32 result, bf16 result)."""
+    if "v" not in _BLEND_ERR:
+        import engine
+        import workload
+        cells, tm, mc = workload.make_positions(G, seed=3)
+        p = engine.make_params(1, 1.8, planner_steps=5, difficulty="hard", deterministic=True)
+        out = []
+        for prec in (0, 1):
+            e = engine.Engine(max_games=G, max_simulations=8, precision=prec)
+            e.set_pv_weights(weights["pv"])
+            e.set_planner_weights(weights["graphnet"], weights["dqn"])
+            r = e.planner_move(e.boards_from_cells(cells, tm, mc), tm, p)
+            out.append({k: v.cpu().numpy() for k, v in r.items()})
+            e.close()
+        valid = out[0]["topk"] >= 0
+        err = float(np.max(np.abs(out[0]["composed"] - out[1]["composed"])[valid]))
+        _BLEND_ERR["v"] = (err, out[0], out[1])
+    return _BLEND_ERR["v"]

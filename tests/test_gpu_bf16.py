@@ -74,13 +74,20 @@ def test_search_trees_do_not_depend_on_precision(engines):
         assert np.array_equal(a, b)
 
 
-def test_det_b_search_bf16_vs_reference(engines):
-    """Planner-guided searches in bf16: the blended pick may flip on near-ties, so allow a few trees
-    to differ; the rest must be bit-exact against the reference goldens."""
+def test_det_b_search_bf16_vs_reference(engines, weights):
+    """Planner-guided deterministic searches in bf16 against the reference's own trees (mcts_planner.npz).  The
+    blended pick reads GraphNet / DQN outputs, so a tree may differ only where two candidates were closer than twice
+    the measured bf16 error of the blended score: tests/golden/oracle_gaps.npz holds, per tree, the smallest top-2 gap
+    the pinned oracle saw over all of the tree's picks.  Every differing tree must contain such a near-tie, and every
+    tree without one must be bit-exact."""
     import engine
+    from conftest import bf16_blend_error, report
     _, b16 = engines
     g = golden("mcts_planner")
-    bad = 0
+    gaps = golden("oracle_gaps")["min_gap"]
+    err = bf16_blend_error(weights)[0]
+    assert err < 2e-2                                        # north_star: 2e-2 in bf16
+    bad = []
     for i in range(len(g["sims"])):
         p = engine.make_params(int(g["sims"][i]), float(g["c_puct"][i]), beta=float(g["beta"][i]),
                                planner_steps=int(g["planner_steps"][i]), difficulty=str(g["difficulty"][i]),
@@ -91,5 +98,7 @@ def test_det_b_search_bf16_vs_reference(engines):
         n = int(g["n_nodes"][i])
         if not (len(t["visits"]) == n and np.array_equal(t["visits"], g["visits"][i][:n])
                 and np.array_equal(t["value"], g["value"][i][:n])):
-            bad += 1
-    assert bad <= len(g["sims"]) // 3, bad
+            bad.append(i)
+    report("det_b_bf16", dict(trees=len(g["sims"]), differing=bad, gaps_of_differing=[float(gaps[i]) for i in bad],
+                              blend_err=err, near_tie_trees=int(np.sum(gaps < 2 * err))))
+    assert all(gaps[i] < 2 * err for i in bad), [(i, float(gaps[i])) for i in bad]

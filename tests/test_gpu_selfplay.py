@@ -91,3 +91,28 @@ def test_stochastic_selfplay_statistics(weights):
     assert len(firsts) > 50                                            # book plies are randomised per game
     # epsilon = 0.5: about half of the searched plies are uniform random moves, so games differ
     assert len({tuple(int(p["move"]) for p in plies[6:12]) for plies in games.values()}) > 100
+
+
+def test_games_total_plays_exactly_the_first_n_starts(weights):
+    """gz_selfplay_begin(games_total = N): the N games with start ordinal generation * G + slot < N are played to the
+    end and recorded -- the reference's `for game in range(N): play_one_game` (training.py:415-420) -- whatever their
+    length; games started later only keep their slot busy (an open-ended session stopped at N finishers would keep
+    whichever games ended first)."""
+    import ai_agent
+    import selfplay
+    G, N = 64, 160
+    ai = ai_agent.AlphaZeroGomokuAI(1, "easy", device="cuda", planner_steps=0, seed=21, precision="bf16")
+    ai.params["num_simulations"] = 8
+    sp = selfplay.SelfPlay(ai, G, seed=4, games_total=N)
+    rec = sp.play_games(max_steps=2000)
+    st = sp.stats()
+    assert st["games_finished"] == N and st["records_dropped"] == 0
+    games = selfplay.split_games(rec)
+    want = {slot + (gen << 20) for gen in range(3) for slot in range(G) if gen * G + slot < N}
+    assert set(games) == want and len(want) == N
+    for plies in games.values():
+        b, _, _ = _replay_game(plies)
+        assert b.game_over
+    assert st["plies_played"] == len(rec) == sum(len(p) for p in games.values())
+    sp.step(3)                                              # later games are neither counted nor recorded
+    assert sp.stats()["games_finished"] == N and len(sp.drain()) == 0

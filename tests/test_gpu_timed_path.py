@@ -67,22 +67,11 @@ def test_config3_stochastic_trees_fp32_bit_exact_vs_oracle(weights):
 
 
 def test_config3_bf16_blend_error_and_tree_accounting(weights):
-    import engine
-    import workload
+    from conftest import bf16_blend_error
     g = golden("oracle_config3")
     G = 4096
-    cells, tm, mc = workload.make_positions(G, seed=3)
-    p = engine.make_params(1, 1.8, planner_steps=5, difficulty="hard", deterministic=True)
-    out = []
-    for prec in (0, 1):
-        e = _engine(weights, prec, G, 8)
-        r = e.planner_move(e.boards_from_cells(cells, tm, mc), tm, p)
-        out.append({k: v.cpu().numpy() for k, v in r.items()})
-        e.close()
-    f32, b16 = out
+    err, f32, b16 = bf16_blend_error(weights, G)
     assert np.array_equal(f32["topk"], b16["topk"]) and np.array_equal(f32["scores2"], b16["scores2"])   # integer work
-    valid = f32["topk"] >= 0
-    err = float(np.max(np.abs(f32["composed"] - b16["composed"])[valid]))
     assert err < 2e-2                                                     # north_star: 2e-2 in bf16
     flips = np.flatnonzero(f32["move"] != b16["move"])
     worst = 0.0

@@ -136,3 +136,34 @@ def test_mcts_det_b_whole_trees(oracle):
     """DET-B (planner-guided playouts).  The blended f32 pick may flip on a near-tie."""
     g = golden("mcts_planner")
     assert _check_trees(oracle, g, allow_near_tie_flips=True) <= 1
+
+
+def test_oracle_fixtures_are_current(oracle):
+    """tests/golden/oracle_*.npz were written by the oracle itself (make_oracle_fixtures.py: minutes of CPU per tree).
+    A tree of S simulations begins with the tree of S' < S simulations (one node per simulation, same Philox counters),
+    so a 10-simulation re-run pins positions, seed, game ids and parameters of the committed S = 200 trees; the
+    outcome-rate fixture is re-sampled with other game ids and must agree within its binomial bound."""
+    import oracle as orc
+    from make_oracle_fixtures import C3, STOCH
+    g = golden("oracle_config3")
+    assert len(g["index"]) >= 128
+    for k in (0, 41, 127):
+        b = orc.board_from_cells(g["cells"][k], g["to_move"][k], g["move_count"][k])
+        p = oracle.params(10, C3["c_puct"], C3["beta"], C3["planner_steps"], int(g["to_move"][k]), C3["difficulty"])
+        t = oracle.search(b, p, seed=C3["seed"], game=C3["game_base"] + k)
+        n = len(t["parent"])
+        assert np.array_equal(t["parent"], g["parent"][k][:n]) and np.array_equal(t["move"], g["move"][k][:n])
+    s = golden("oracle_stoch")
+    n_r = int(s["n"])
+    assert np.all(s["counts"].sum(-1) == n_r) and n_r >= 100000
+    i, n_e = 6, 3000
+    b = orc.board_from_cells(s["cells"][i], s["to_move"][i], s["move_count"][i])
+    p = oracle.params(1, 1.8, 0.2, 0, int(s["to_move"][i]), "hard")
+    cnt = np.zeros(4)
+    for j in range(n_e):
+        v, _, _ = oracle.simulate(b, p, orc.Rng(1, 99, 7, 10 ** 6 + j, i))
+        cnt[{1.0: 0, -1.0: 1, 0.1: 2, 0.0: 3}[v]] += 1
+    for k in range(4):
+        pe, pr = cnt[k] / n_e, s["counts"][0][i][k] / n_r
+        pool = (cnt[k] + s["counts"][0][i][k]) / (n_e + n_r)
+        assert abs(pe - pr) <= 3.9 * np.sqrt(max(pool * (1 - pool), 1e-6) * (1 / n_e + 1 / n_r))

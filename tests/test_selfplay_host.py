@@ -87,3 +87,94 @@ def test_game_sharding_ids_are_global():
     ids = [selfplay.game_id(r, G, g, k) for r in range(W) for g in (0, 1, G - 1) for k in range(4)]
     assert len(set(ids)) == len(ids) and max(ids) < 2 ** 32
     assert selfplay.game_id(7, G, G - 1, 0) < 2 ** 20
+
+
+# ---- data-parallel update (training.run_iteration update="dp"): world-size-2 gloo, CPU ---------------------------------
+def _dp_worker(rank, world, port, q):
+    from conftest import GOLDEN
+    sys.path[:0] = [PKG, GOLDEN]
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    import training
+    from neural_network import GomokuModel
+    from weights import make_state_dict
+    g = torch.Generator().manual_seed(5)
+    n = 96
+    x = (torch.rand(n, 3, 15, 15, generator=g) > 0.6).float()
+    y = torch.randint(0, 225, (n,), generator=g)
+    v = torch.randint(-1, 2, (n,), generator=g).float()
+
+    class Data:
+        planes, move, value = x, y, v
+
+        def batch(self, ids):
+            i = torch.as_tensor(ids, dtype=torch.long)
+            return x[i], y[i], v[i].reshape(-1, 1)
+    m = GomokuModel(device="cpu")
+    m.model.load_state_dict({k: torch.from_numpy(np.asarray(t)) for k, t in make_state_dict("pv", 1234).items()})
+    opt = torch.optim.Adam(m.model.parameters(), lr=8e-4, weight_decay=1e-5)
+    order = list(range(n - 3))                                   # ragged last global batch: 93 = 2 * 32 + 29
+    mine, local_b = training.shard_batches(order, 32, rank, world)
+    loader = training.DeviceLoader(Data(), mine, local_b, shuffle=False)
+    tl = training.train_epoch(m, loader, opt, "cpu", 0.8, 1, 1, world, None)
+    vl = training.validate_epoch(m, loader, "cpu", 1, 1, world, None)
+    q.put((rank, tl, vl, mine, {k: t.numpy().copy() for k, t in m.model.state_dict().items()}))
+    dist.destroy_process_group()
+
+
+def test_data_parallel_update_world_size_2_gloo(weights):
+    """Each rank trains on its half of every global batch; after one all-reduce per step both ranks must hold the same
+    weights, and they must equal a single process that averages the two half-batch gradients by hand."""
+    import torch
+    import torch.multiprocessing as mp
+    import training
+    from neural_network import GomokuModel
+    port = 31500 + os.getpid() % 2000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_dp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted((q.get(timeout=300) for _ in ps), key=lambda r: r[0])
+    for p in ps:
+        p.join(timeout=60)
+    (_, tl0, vl0, idx0, sd0), (_, tl1, vl1, idx1, sd1) = res
+    assert tl0 == tl1 and vl0 == vl1                              # the mean over all ranks' batches, on every rank
+    assert len(idx0) == len(idx1) == 16 + 16 + 14 and not set(idx0) & set(idx1)
+    assert idx0[:16] == list(range(16)) and idx1[:16] == list(range(16, 32))
+    for k in sd0:
+        if "running" not in k and "num_batches" not in k:         # BatchNorm statistics are rank-local until averaged
+            assert np.array_equal(sd0[k], sd1[k]), k
+    # the same three steps by hand in one process
+    torch.set_num_threads(1)
+    g = torch.Generator().manual_seed(5)
+    n = 96
+    x = (torch.rand(n, 3, 15, 15, generator=g) > 0.6).float()
+    y = torch.randint(0, 225, (n,), generator=g)
+    v = torch.randint(-1, 2, (n,), generator=g).float()
+    m = GomokuModel(device="cpu")
+    m.model.load_state_dict({k: torch.from_numpy(np.asarray(t)) for k, t in weights["pv"].items()})
+    twin = GomokuModel(device="cpu")                              # rank 1's BatchNorm statistics evolve separately
+    twin.model.load_state_dict(m.model.state_dict())
+    opt = torch.optim.Adam(m.model.parameters(), lr=8e-4, weight_decay=1e-5)
+    m.train_mode(); twin.train_mode()
+    for b in range(3):
+        grads = []
+        for net, idx in ((m, idx0), (twin, idx1)):
+            lo = [0, 16, 32][b]
+            ids = torch.as_tensor(idx[lo:lo + (16 if b < 2 else 14)])
+            net.model.zero_grad()
+            with torch.no_grad():
+                for pt, ps_ in zip(twin.model.parameters(), m.model.parameters()):
+                    pt.copy_(ps_)
+            training._losses(net, x[ids], y[ids], v[ids].reshape(-1, 1)).backward()
+            grads.append([p.grad.clone() for p in net.model.parameters()])
+        for p, g0, g1 in zip(m.model.parameters(), grads[0], grads[1]):
+            p.grad = (g0 + g1) / 2
+        torch.nn.utils.clip_grad_norm_(m.model.parameters(), 0.8)
+        opt.step()
+    for (k, t), p in zip(m.model.named_parameters(), m.model.parameters()):
+        assert np.allclose(sd0[k], p.detach().numpy(), rtol=0, atol=1e-6), k
