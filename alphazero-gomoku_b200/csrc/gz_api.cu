@@ -207,6 +207,25 @@ static void pack_conv_bf16(std::vector<uint16_t> &out, const float *w, const flo
                     }
                 }
 }
+// GraphNet 3x3 64 -> 64 weights for k_gn_block_pairs: three pair blocks [8 cg][128 rows][8 ch] -- rows 0-63 = tap
+// (ty, dx = 0), rows 64-127 = tap (ty, dx = -1) -- then three single blocks [8 cg][64][8 ch] = tap (ty, dx = +1)
+static void pack_gn3x3_pairs(std::vector<uint16_t> &out, const float *w) {
+    size_t base = out.size();
+    out.resize(base + (size_t)9 * 64 * 64);
+    size_t o = base;
+    for (int ty = 0; ty < 3; ++ty)
+        for (int cg = 0; cg < 8; ++cg)
+            for (int r = 0; r < 128; ++r)
+                for (int j = 0; j < 8; ++j) {
+                    const int co = r & 63, tap = 3 * ty + (r < 64 ? 1 : 0), ci = cg * 8 + j;
+                    out[o++] = f2bf(w[((size_t)co * 64 + ci) * 9 + tap]);
+                }
+    for (int ty = 0; ty < 3; ++ty)
+        for (int cg = 0; cg < 8; ++cg)
+            for (int co = 0; co < 64; ++co)
+                for (int j = 0; j < 8; ++j)
+                    out[o++] = f2bf(w[((size_t)co * 64 + cg * 8 + j) * 9 + 3 * ty + 2]);
+}
 // input convolution [cout][3][3][3] (+ BN) -> per tap [2 channel groups][cout][8 channels] bf16 with
 // channels 0..2 = black / white / empty and the other 13 zero (FROM_BOARD mode of k_conv_umma)
 static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const float *bn, int cout) {
@@ -358,9 +377,11 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         memcpy(e->bw.gn_host_head, &pk.host[o[18]], 128 * sizeof(float));
         memcpy(e->bw.gn_host_head + 128, &pk.host[o[19]], 2 * sizeof(float));
         std::vector<uint16_t> bf;
-        size_t o3[4], o1[4];
+        size_t o3[4], o1[4], o3p[4];
         const float *q = gnf + 1728 + 64;
         for (int i = 0; i < 4; ++i) {
+            o3p[i] = bf.size() * 2;
+            pack_gn3x3_pairs(bf, q);
             o3[i] = bf.size() * 2;
             pack_conv_bf16(bf, q, nullptr, 64, 64, 3); q += 36864 + 64;
             o1[i] = bf.size() * 2;
@@ -370,7 +391,10 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         pack_conv0_bf16(bf, gnf, nullptr, 64);
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.gn_blob);
         if (rc) return rc;
-        for (int i = 0; i < 4; ++i) { e->bw.gn_l3_w[i] = e->bw.gn_blob + o3[i]; e->bw.gn_l1_w[i] = e->bw.gn_blob + o1[i]; }
+        for (int i = 0; i < 4; ++i) {
+            e->bw.gn_l3_w[i] = e->bw.gn_blob + o3[i]; e->bw.gn_l1_w[i] = e->bw.gn_blob + o1[i];
+            e->bw.gn_l3p_w[i] = e->bw.gn_blob + o3p[i];
+        }
         e->bw.gn_embed_w = e->bw.gn_blob + off0;
         {   // head FC 450 -> 225 for gz_nn_fc.cu
             const float *hfc_w = gnf + 1728 + 64 + 4 * (36864 + 64 + 4096 + 64) + 128 + 2, *hfc_b = hfc_w + 101250;
@@ -675,6 +699,18 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
     // two to four lanes measure within 2 % of one (profiles/r01_lanes.md); more lanes stay available on request
     int nl = e->cfg.lanes > 0 ? e->cfg.lanes : 1;
     if (nl > G / 128) nl = G / 128 > 1 ? G / 128 : 1;   // every lane owns at least one whole tile of 128 boards
+    // Small batches are launch-bound (~50 kernels per wave, microseconds of work each: AlphaZeroGomokuAI.get_move on
+    // one board): wave 0 runs eagerly, one wave is captured into a CUDA graph whose kernels read the simulation index
+    // from device memory, and the graph is replayed for the remaining simulations.  The legacy default stream cannot
+    // be captured: the search then runs on the engine's own stream, ordered after / before the caller's by events.
+    const bool graphed = nl == 1 && !e->profiling && G <= kGraphMaxGames && c.S >= 4 && !e->no_graph;
+    cudaStream_t s_user = s;
+    const bool redirect = graphed && (s == nullptr || s == cudaStreamLegacy || s == cudaStreamPerThread);
+    if (redirect) {
+        CK(cudaEventRecord(e->lane_go, s_user));
+        s = e->own_stream;
+        CK(cudaStreamWaitEvent(s, e->lane_go, 0));
+    }
     Engine *v[kMaxLanes];
     cudaStream_t ls[kMaxLanes];
     int g0[kMaxLanes + 1];
@@ -714,10 +750,6 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
         return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count() > p->time_limit_s;
     };
     int done = 0;   // simulations started
-    // Small batches are launch-bound (~50 kernels per wave, microseconds of work each: AlphaZeroGomokuAI.get_move on
-    // one board): wave 0 runs eagerly, one wave is captured into a CUDA graph whose kernels read the simulation index
-    // from device memory, and the graph is replayed for the remaining simulations.
-    const bool graphed = nl == 1 && !e->profiling && G <= kGraphMaxGames && c.S >= 4 && !e->no_graph;
     if (graphed) {
         wave(0, lc);
         done = 1;
@@ -732,7 +764,7 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
         wave(-1, &gc);
         launch_set_sim(e->d_sim, 1, 1, s);
         cudaError_t ce = cudaStreamEndCapture(s, &graph);
-        if (ce != cudaSuccess) return fail(GZ_ERR_CUDA, "gz_search: graph capture: %s", cudaGetErrorString(ce));
+        if (ce != cudaSuccess) { cudaGetLastError(); return fail(GZ_ERR_CUDA, "gz_search: graph capture: %s", cudaGetErrorString(ce)); }
         const int64_t per_wave = e->launches - before + 1;   // + the set_sim node
         e->launches = before;                                // nothing ran during the capture
         ce = cudaGraphInstantiate(&exec, graph, 0);
@@ -771,6 +803,10 @@ static int search_device(Engine *e, const gz_board *d_boards, const uint8_t *d_a
             CK(cudaEventRecord(e->lane_done[l], ls[l]));
             CK(cudaStreamWaitEvent(s, e->lane_done[l], 0));
         }
+    }
+    if (redirect) {
+        CK(cudaEventRecord(e->lane_done[0], s));
+        CK(cudaStreamWaitEvent(s_user, e->lane_done[0], 0));
     }
     CKL();
     e->searched = true;

@@ -70,6 +70,7 @@ struct Bf16Weights {
     float gn_host_head[130];      // GraphNet head 1x1: w[64][2] (device layout of hconv_w), b[2]
     uint8_t *pv_tower_w[4];
     uint8_t *gn_l3_w[4];
+    uint8_t *gn_l3p_w[4];   // the same 3x3 weights in k_gn_block_pairs' order: 3 x [dx=0 | dx=-1] stacked along N, 3 x dx=+1
     uint8_t *gn_l1_w[4];
     uint8_t *pv_conv0_w, *gn_embed_w;   // input convolutions, [tap][2 cg][cout][8]
     uint8_t *pv_blob, *gn_blob;

@@ -472,59 +472,73 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
             ptx::mbar_wait(w_full, 0);
             GN_T(const long long w_w = clock64() - tk0;)
             const uint32_t w3_addr = ptx::smem_u32(sw3), w1_addr = ptx::smem_u32(sw1);
-            for (int it = 0; it <= n_it; ++it) {
-                if (it < n_it) {
-                    const int ab = it & 1;
-                    const uint32_t par = (it >> 1) & 1;
-                    GN_T(long long t0 = clock64();)
-                    ptx::mbar_wait(&d1_empty[ab], par ^ 1);
-                    GN_T(long long t1 = clock64(); w_d1e += t1 - t0;)
-                    ptx::mbar_wait(&a_full[ab], par);
-                    GN_T(long long t2 = clock64(); w_af += t2 - t1;)
-                    ptx::tc_fence_after();
-                    // Descriptors = one base per operand + compile-time constants in the 16-byte address field:
-                    // at N = 64 a UMMA lasts 48 cycles and anything more per instruction shows (the loop is fully
-                    // unrolled: 72 instructions, two 64-bit adds each).
-                    const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
-                    const uint64_t db0 = ptx::make_desc(w3_addr, LBO_B, 128);
-                    const uint32_t acc = tmem_base + ab * 128;
-                    const uint32_t acc_h = acc + h * 64;
-                    const uint64_t da_h = da0 + (uint64_t)(128 * h);
+            const uint64_t db0 = ptx::make_desc(w3_addr, LBO_B, 128);
+            const uint64_t dw0 = ptx::make_desc(w1_addr, LBO_B, 128);
+            // The tensor pipe takes UMMAs from a shallow queue: issuing the 36 instructions of a board's 3x3 blocks this
+            // warp for most of their execution time (measured: 2.9 k of 3.9 k cycles per board), and everything it did
+            // BETWEEN boards -- four mbarrier waits at ~60-150 cycles each even when already satisfied, the 1x1's four
+            // UMMAs, four commits -- was a bubble both issuers hit at the same moment.  So the per-board work is software
+            // pipelined into the 3x3's instruction stream, where it costs nothing while the queue is full:
+            //   taps 0-3 of board it | 1x1 of board it-1 (its A operand was packed by epilogue 1 long ago) |
+            //   taps 4-7 | the waits for board it+1's accumulator and slab | tap 8 | commits
+            // and the next board's first UMMA follows the commits directly.
+            auto wait_board = [&](int it) {
+                const int ab = it & 1;
+                const uint32_t par = (it >> 1) & 1;
+                GN_T(long long t0 = clock64();)
+                ptx::mbar_wait(&d1_empty[ab], par ^ 1);
+                GN_T(long long t1 = clock64(); w_d1e += t1 - t0;)
+                ptx::mbar_wait(&a_full[ab], par);
+                GN_T(w_af += clock64() - t1;)
+                ptx::tc_fence_after();
+            };
+            auto issue_1x1 = [&](int j) {
+                const int jb = j & 1;
+                const uint32_t par = (j >> 1) & 1;
+                GN_T(long long t0 = clock64();)
+                ptx::mbar_wait(&mid_full[jb], par);
+                GN_T(long long t1 = clock64(); w_mf += t1 - t0;)
+                ptx::mbar_wait(&d2_empty[jb], par ^ 1);
+                GN_T(long long t2 = clock64(); w_d2e += t2 - t1;)
+                ptx::tc_fence_after();
+                // A = the 3x3 result packed to bf16 in place in its accumulator columns (epilogue 1): TS form
+                const uint32_t acc = tmem_base + 256 + jb * 128;
+                const uint32_t amid = tmem_base + jb * 128;
 #pragma unroll
-                    for (int tap = 0; tap < 9; ++tap) {
-                        const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            ptx::umma_bf16_elect(acc_h, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff),
-                                                 db0 + (uint64_t)((tap * 8192 + 2 * k * (int)LBO_B) >> 4),
-                                                 idesc, (tap | k) != 0);
-                    }
-                    ptx::umma_commit_elect(&a_empty[ab]);
-                    ptx::umma_commit_elect(&d1_full[ab]);
-                    GN_T(t_i3 += clock64() - t2;)
+                for (int k = 0; k < 4; ++k)
+                    ptx::umma_bf16_ts_elect(acc + h * 64, amid + h * 64 + 8 * k,
+                                            dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
+                ptx::umma_commit_elect(&mid_empty[jb]);
+                ptx::umma_commit_elect(&d2_full[jb]);
+                GN_T(t_i1 += clock64() - t2;)
+            };
+            if (n_it > 0) wait_board(0);
+            for (int it = 0; it < n_it; ++it) {
+                const int ab = it & 1;
+                GN_T(long long t2 = clock64();)
+                // Descriptors = one base per operand + compile-time constants in the 16-byte address field: anything more
+                // per instruction shows at ~40 cycles per UMMA (fully unrolled: 36 instructions, two 64-bit adds each).
+                const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
+                const uint32_t acc_h = tmem_base + ab * 128 + h * 64;
+#define GZ_GN_TAPS(T0, T1)                                                                                         \
+                _Pragma("unroll") for (int tap = T0; tap < T1; ++tap) {                                            \
+                    const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);                                    \
+                    _Pragma("unroll") for (int k = 0; k < 4; ++k)                                                  \
+                        ptx::umma_bf16_elect(acc_h, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff),              \
+                                             db0 + (uint64_t)((tap * 8192 + 2 * k * (int)LBO_B) >> 4), idesc,       \
+                                             (tap | k) != 0);                                                      \
                 }
-                if (it > 0) {
-                    const int j = it - 1, jb = j & 1;
-                    const uint32_t par = (j >> 1) & 1;
-                    GN_T(long long t0 = clock64();)
-                    ptx::mbar_wait(&mid_full[jb], par);
-                    GN_T(long long t1 = clock64(); w_mf += t1 - t0;)
-                    ptx::mbar_wait(&d2_empty[jb], par ^ 1);
-                    GN_T(long long t2 = clock64(); w_d2e += t2 - t1;)
-                    ptx::tc_fence_after();
-                    // A = the 3x3 result packed to bf16 in place in its accumulator columns (epilogue 1): TS form
-                    const uint64_t dw0 = ptx::make_desc(w1_addr, LBO_B, 128);
-                    const uint32_t acc = tmem_base + 256 + jb * 128;
-                    const uint32_t amid = tmem_base + jb * 128;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        ptx::umma_bf16_ts_elect(acc + h * 64, amid + h * 64 + 8 * k,
-                                                dw0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, k != 0);
-                    ptx::umma_commit_elect(&mid_empty[jb]);
-                    ptx::umma_commit_elect(&d2_full[jb]);
-                    GN_T(t_i1 += clock64() - t2;)
-                }
+                GZ_GN_TAPS(0, 4)
+                if (it > 0) issue_1x1(it - 1);
+                GZ_GN_TAPS(4, 8)
+                if (it + 1 < n_it) wait_board(it + 1);
+                GZ_GN_TAPS(8, 9)
+#undef GZ_GN_TAPS
+                ptx::umma_commit_elect(&a_empty[ab]);
+                ptx::umma_commit_elect(&d1_full[ab]);
+                GN_T(t_i3 += clock64() - t2;)
             }
+            if (n_it > 0) issue_1x1(n_it - 1);
             GN_T(if (blockIdx.x == 0 && lane == 0 && n_it > 0)
                      printf("gn issuer h=%d: %d boards, total %lld | per board: wait d1_empty %lld, a_full %lld, issue3x3 %lld, wait mid_full %lld, d2_empty %lld, issue1x1 %lld | weights %lld\n",
                             h, n_it, clock64() - tk0, w_d1e / n_it, w_af / n_it, t_i3 / n_it, w_mf / n_it, w_d2e / n_it, t_i1 / n_it, w_w);)
@@ -537,34 +551,8 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
         const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 64;
         GN_T(long long w_d1f = 0, w_me = 0, t_e1 = 0, w_d2f = 0, t_e2 = 0;)
         for (int it = 0; it <= n_it; ++it) {
-            if (it < n_it) {
-                const int ab = it & 1;
-                const uint32_t par = (it >> 1) & 1;
-                GN_T(long long t0 = clock64();)
-                ptx::mbar_wait(&d1_full[ab], par);
-                GN_T(long long t1 = clock64(); w_d1f += t1 - t0;)
-                ptx::mbar_wait(&mid_empty[ab], par ^ 1);
-                GN_T(long long t2 = clock64(); w_me += t2 - t1;)
-                ptx::tc_fence_after();
-                // bias + ReLU + bf16 pack, written back IN PLACE over the accumulator's first 32 columns (the write
-                // cursor c0/2 never passes the read cursor c0): the 1x1 reads it as its A operand from TMEM
-#pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
-                    float v[16];
-                    ptx::tmem_ld16(tlane + ab * 128 + c0, v);
-                    uint32_t pk[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + kc.b3[c0 + 2 * i], 0.f),
-                                               fmaxf(v[2 * i + 1] + kc.b3[c0 + 2 * i + 1], 0.f));
-                    ptx::tmem_st8(tlane + ab * 128 + c0 / 2, pk);
-                }
-                ptx::tmem_wait_st();
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
-                GN_T(t_e1 += clock64() - t2;)
-            }
+            // the 1x1 of board it-1 ran in the middle of board it's 3x3: its epilogue first, so that this warp is
+            // free the moment the 3x3 completes (epilogue 1 is what the issuers wait for next)
             if (it > 0) {
                 const int j = it - 1, jb = j & 1;
                 const int b = blockIdx.x + j * gridDim.x;
@@ -610,6 +598,34 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
                 if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
                 GN_T(t_e2 += clock64() - t1;)
             }
+            if (it < n_it) {
+                const int ab = it & 1;
+                const uint32_t par = (it >> 1) & 1;
+                GN_T(long long t0 = clock64();)
+                ptx::mbar_wait(&d1_full[ab], par);
+                GN_T(long long t1 = clock64(); w_d1f += t1 - t0;)
+                ptx::mbar_wait(&mid_empty[ab], par ^ 1);
+                GN_T(long long t2 = clock64(); w_me += t2 - t1;)
+                ptx::tc_fence_after();
+                // bias + ReLU + bf16 pack, written back IN PLACE over the accumulator's first 32 columns (the write
+                // cursor c0/2 never passes the read cursor c0): the 1x1 reads it as its A operand from TMEM
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
+                    ptx::tmem_ld16(tlane + ab * 128 + c0, v);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        pk[i] = ptx::pack_bf16(fmaxf(v[2 * i] + kc.b3[c0 + 2 * i], 0.f),
+                                               fmaxf(v[2 * i + 1] + kc.b3[c0 + 2 * i + 1], 0.f));
+                    ptx::tmem_st8(tlane + ab * 128 + c0 / 2, pk);
+                }
+                ptx::tmem_wait_st();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
+                GN_T(t_e1 += clock64() - t2;)
+            }
         }
         GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 2 || warp == 9) && n_it > 0)
                  printf("gn epilogue warp %d: per board: wait d1_full %lld, mid_empty %lld, epi1 %lld, wait d2_full %lld, epi2 %lld\n",
@@ -620,20 +636,318 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
 }
 
-static void launch_gn_block(Engine &e, const uint8_t *in, const uint8_t *w3, const uint8_t *w1, int block,
-                            uint8_t *out, uint8_t *head_out, int G, cudaStream_t s) {
+// ------------------------------------------------------------------------------------------------
+// k_gn_block_pairs: the same block with TWO taps per UMMA where the geometry allows it.
+//
+// k_gn_block is bound by the shared-memory operand fetches of its N = 64 UMMAs (A 4 KB + B 2 KB per instruction,
+// ~40 cycles measured against 32 of math).  The A tiles of the nine taps are row-shifted views of one slab, so two taps
+// can share one A fetch if their weights are stacked along N (N = 128: 8 KB for two taps instead of 12 KB, 64 cycles =
+// the math rate): with A read at the offset of tap (dy, dx = 0), columns 0-63 accumulate that tap for output row m,
+// and columns 64-127 accumulate W(dy, dx = -1) * slab[m + off(dy, 0)], which is tap (dy, -1)'s contribution to output
+// row m + 1.  Epilogue 1 therefore adds D_b[m - 1] to D_a[m]: one lane shuffle, and NO exchange between warps, because
+// lane 0 of every epilogue warp sits on board column 0 (tile row = multiple of 32 -> plane position = multiple of
+// 16), whose left neighbour is the zero padding column: the missing term is exactly zero.  The dx = +1 taps stay
+// single (N = 64).  Per board and M half: 12 N = 128 + 12 N = 64 UMMAs instead of 36 N = 64 (operand wavefronts -22 %).
+//
+// Tensor memory (512 columns): per (M half, buffer) 128 columns = [D_a | D_b].  The 1x1's accumulator D2 reuses the
+// D_b columns of its own buffer once epilogue 1 has consumed them; epilogue 2 zeroes them again after reading D2, so
+// that every pair UMMA accumulates (the first single of a board initialises D_a alone: a pair cannot initialise one
+// half of its 128 columns and accumulate into the other).  Singles are issued first, which gives epilogue 2 of the
+// board two back the time it needs before the pairs touch D_b.
+struct GnPairsCfg {
+    static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
+    static constexpr int PAIR_BYTES = 8 * 128 * 16, SINGLE_BYTES = 8 * 64 * 16;
+    static constexpr int W3_BYTES = 3 * PAIR_BYTES + 3 * SINGLE_BYTES, W1_BYTES = 8 * 64 * 16;
+    static constexpr int SMEM = 2 * SLAB_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
+};
+
+// two x16 loads in flight, one wait
+__device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, float *va, float *vb) {
+    uint32_t a[16], b[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]), "=r"(a[8]),
+          "=r"(a[9]), "=r"(a[10]), "=r"(a[11]), "=r"(a[12]), "=r"(a[13]), "=r"(a[14]), "=r"(a[15])
+        : "r"(ta) : "memory");
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7]), "=r"(b[8]),
+          "=r"(b[9]), "=r"(b[10]), "=r"(b[11]), "=r"(b[12]), "=r"(b[13]), "=r"(b[14]), "=r"(b[15])
+        : "r"(tb) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                   "+r"(a[8]), "+r"(a[9]), "+r"(a[10]), "+r"(a[11]), "+r"(a[12]), "+r"(a[13]), "+r"(a[14]), "+r"(a[15])
+                 : : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]),
+                   "+r"(b[8]), "+r"(b[9]), "+r"(b[10]), "+r"(b[11]), "+r"(b[12]), "+r"(b[13]), "+r"(b[14]), "+r"(b[15])
+                 : : "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { va[i] = __uint_as_float(a[i]); vb[i] = __uint_as_float(b[i]); }
+}
+
+template <bool FINAL>
+__global__ void __launch_bounds__(352, 1)
+k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
+                 const __grid_constant__ GnBlockConsts kc, uint8_t *__restrict__ out_planes,
+                 uint8_t *__restrict__ head_out, int G) {
+    using C = GnPairsCfg;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *slab = smem;
+    uint8_t *sw3 = slab + 2 * C::SLAB_BYTES;      // [3 pair blocks: 8 cg x 128 rows x 16 B][3 single blocks: 8 cg x 64 x 16 B]
+    uint8_t *sw1 = sw3 + C::W3_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sw1 + C::W1_BYTES + 2 * 64 * 4);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *d1_full = bars + 4, *d1_empty = bars + 6;
+    uint64_t *mid_full = bars + 8, *mid_empty = bars + 10, *d2_full = bars + 12, *d2_empty = bars + 14;
+    uint64_t *w_full = bars + 16;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 17);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {   // every tcgen05.commit comes twice: one per issuer warp (M half)
+            ptx::mbar_init(&a_full[i], 1);   ptx::mbar_init(&a_empty[i], 2);
+            ptx::mbar_init(&d1_full[i], 2);  ptx::mbar_init(&d1_empty[i], 8);
+            ptx::mbar_init(&mid_full[i], 8); ptx::mbar_init(&mid_empty[i], 2);
+            ptx::mbar_init(&d2_full[i], 2);  ptx::mbar_init(&d2_empty[i], 8);
+        }
+        ptx::mbar_init(w_full, 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int n_it = blockIdx.x < G ? (G - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+    // accumulator block of (buffer ab, M half h): 128 columns [D_a | D_b]
+    auto acc_of = [&](int ab, int h) { return tmem_base + (uint32_t)(ab * 256 + h * 128); };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            ptx::mbar_expect_tx(w_full, C::W3_BYTES + C::W1_BYTES);
+            for (int t = 0; t < 9; ++t) ptx::bulk_g2s(sw3 + t * 8192, w3 + t * 8192, 8192, w_full);
+            ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
+            for (int it = 0; it < n_it; ++it) {
+                const int b = blockIdx.x + it * gridDim.x, ab = it & 1;
+                ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+                ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
+                const uint8_t *src = in_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes - 16;
+                for (int cg = 0; cg < 8; ++cg)
+                    ptx::bulk_g2s(slab + ab * C::SLAB_BYTES + cg * C::SLAB_ROWS * 16,
+                                  src + (size_t)cg * kPlaneBytes, C::SLAB_ROWS * 16, &a_full[ab]);
+            }
+        }
+    } else if (warp == 1 || warp == 10) {
+        const int h = warp == 1 ? 0 : 1;
+        constexpr uint32_t idesc64 = ptx::make_idesc_bf16(128, 64), idesc128 = ptx::make_idesc_bf16(128, 128);
+        constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_S = 64 * 16, LBO_P = 128 * 16;
+        GN_T(long long tk0 = clock64(); long long w_d1e = 0, w_af = 0, t_i3 = 0, w_mf = 0, w_d2e = 0, t_i1 = 0;)
+        ptx::mbar_wait(w_full, 0);
+        GN_T(const long long w_w = clock64() - tk0;)
+        const uint64_t dpair0 = ptx::make_desc(ptx::smem_u32(sw3), LBO_P, 128);
+        const uint64_t dsing0 = ptx::make_desc(ptx::smem_u32(sw3) + 3 * C::PAIR_BYTES, LBO_S, 128);
+        const uint64_t dw0 = ptx::make_desc(ptx::smem_u32(sw1), LBO_S, 128);
+        auto wait_board = [&](int it) {        // accumulator D_a free (epilogue 1 of board it - 2), slab loaded
+            const int ab = it & 1;
+            const uint32_t par = (it >> 1) & 1;
+            GN_T(long long t0 = clock64();)
+            ptx::mbar_wait(&d1_empty[ab], par ^ 1);
+            GN_T(long long t1 = clock64(); w_d1e += t1 - t0;)
+            ptx::mbar_wait(&a_full[ab], par);
+            GN_T(w_af += clock64() - t1;)
+            ptx::tc_fence_after();
+        };
+        auto issue_1x1 = [&](int j) {          // D2 = the D_b columns of board j's own buffer
+            const int jb = j & 1;
+            GN_T(long long t0 = clock64();)
+            ptx::mbar_wait(&mid_full[jb], (j >> 1) & 1);
+            GN_T(long long t1 = clock64(); w_mf += t1 - t0;)
+            ptx::tc_fence_after();
+            const uint32_t acc = acc_of(jb, h);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                ptx::umma_bf16_ts_elect(acc + 64, acc + 8 * k, dw0 + (uint64_t)((2 * k * (int)LBO_S) >> 4), idesc64, k != 0);
+            ptx::umma_commit_elect(&mid_empty[jb]);
+            ptx::umma_commit_elect(&d2_full[jb]);
+            GN_T(t_i1 += clock64() - t1;)
+        };
+        if (n_it > 0) wait_board(0);
+        for (int it = 0; it < n_it; ++it) {
+            const int ab = it & 1;
+            GN_T(long long t2 = clock64();)
+            const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
+            const uint32_t acc = acc_of(ab, h);
+            // singles first: the dx = +1 taps, N = 64 into D_a; the very first one initialises D_a
+#pragma unroll
+            for (int ty = 0; ty < 3; ++ty) {
+                const int rowoff = 17 + 16 * (ty - 1) + 1;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    ptx::umma_bf16_elect(acc, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff),
+                                         dsing0 + (uint64_t)((ty * C::SINGLE_BYTES + 2 * k * (int)LBO_S) >> 4), idesc64,
+                                         (ty | k) != 0);
+            }
+            // pairs: A at the offset of tap (dy, 0); columns 0-63 += tap (dy, 0), columns 64-127 += tap (dy, -1) for the
+            // NEXT output row.  D_b was zeroed by epilogue 2 of board it - 2 (or at kernel start).
+            GN_T(long long t3 = clock64();)
+            ptx::mbar_wait(&d2_empty[ab], (it >> 1) & 1);
+            GN_T(w_d2e += clock64() - t3;)
+            ptx::tc_fence_after();
+#define GZ_GN_PAIR(TY, K0, K1)                                                                                     \
+            _Pragma("unroll") for (int k = K0; k < K1; ++k)                                                        \
+                ptx::umma_bf16_elect(acc, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + 17 + 16 * (TY - 1)),            \
+                                     dpair0 + (uint64_t)((TY * C::PAIR_BYTES + 2 * k * (int)LBO_P) >> 4), idesc128, 1u);
+            GZ_GN_PAIR(0, 0, 4)
+            GZ_GN_PAIR(1, 0, 4)
+            GZ_GN_PAIR(2, 0, 2)
+            // late enough for epilogue 1 of board it - 1 (two TMEM reads + a shuffle per value: ~1.2 k cycles) to be
+            // through: issued after pair row 1 both issuers sat ~600 cycles in this wait
+            if (it > 0) issue_1x1(it - 1);
+            if (it + 1 < n_it) wait_board(it + 1);
+            GZ_GN_PAIR(2, 2, 4)
+#undef GZ_GN_PAIR
+            ptx::umma_commit_elect(&a_empty[ab]);
+            ptx::umma_commit_elect(&d1_full[ab]);
+            GN_T(t_i3 += clock64() - t2;)
+        }
+        if (n_it > 0) issue_1x1(n_it - 1);
+        GN_T(if (blockIdx.x == 0 && lane == 0 && n_it > 0)
+                 printf("gn(pairs) issuer h=%d: %d boards, total %lld | per board: wait d1_empty %lld, a_full %lld, issue3x3 %lld, wait mid_full %lld, d2_empty %lld, issue1x1 %lld | weights %lld\n",
+                        h, n_it, clock64() - tk0, w_d1e / n_it, w_af / n_it, t_i3 / n_it, w_mf / n_it, w_d2e / n_it, t_i1 / n_it, w_w);)
+    } else {
+        const int q = warp & 3, h = (warp - 2) >> 2;
+        const int row = 128 * h + 32 * q + lane;            // tile row = plane position - 16
+        const int pos = 16 + row;
+        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 128;
+        GN_T(long long w_d1f = 0, w_me = 0, t_e1 = 0, w_d2f = 0, t_e2 = 0;)
+        const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        // D_b of both buffers starts at zero (pair UMMAs only accumulate)
+#pragma unroll
+        for (int ab = 0; ab < 2; ++ab)
+#pragma unroll
+            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(tlane + ab * 256 + 64 + c, zeros);
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { ptx::mbar_arrive(&d2_empty[0]); ptx::mbar_arrive(&d2_empty[1]); }
+        for (int it = 0; it <= n_it; ++it) {
+            if (it > 0) {   // epilogue 2 of board it - 1 (its 1x1 ran in the middle of board it's 3x3)
+                const int j = it - 1, jb = j & 1;
+                const int b = blockIdx.x + j * gridDim.x;
+                GN_T(long long t0 = clock64();)
+                ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
+                GN_T(long long t1 = clock64(); w_d2f += t1 - t0;)
+                ptx::tc_fence_after();
+                const uint32_t td2 = tlane + jb * 256 + 64;
+                if (FINAL) {
+                    float p0 = kc.head_b[0], p1 = kc.head_b[1];
+#pragma unroll
+                    for (int c0 = 0; c0 < 64; c0 += 16) {
+                        float v[16];
+                        ptx::tmem_ld16(td2 + c0, v);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float x = fmaxf(v[i] + kc.b1[c0 + i], 0.f);
+                            p0 = fmaf(kc.head_w[2 * (c0 + i)], x, p0);
+                            p1 = fmaf(kc.head_w[2 * (c0 + i) + 1], x, p1);
+                        }
+                    }
+                    if (valid) {
+                        const int cell = ((pos >> 4) - 1) * 15 + (pos & 15);
+                        store_head_operand(head_out, b, cell, kHeadChunksP, p0);
+                        store_head_operand(head_out, b, kCells + cell, kHeadChunksP, p1);
+                    }
+                } else {
+                    uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
+#pragma unroll
+                    for (int c0 = 0; c0 < 64; c0 += 16) {
+                        float v[16];
+                        ptx::tmem_ld16(td2 + c0, v);
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + kc.b1[c0 + 2 * i], 0.f),
+                                                           fmaxf(v[2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
+                        *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    }
+                }
+                // hand the columns back as a zeroed D_b
+#pragma unroll
+                for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td2 + c, zeros);
+                ptx::tmem_wait_st();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+                GN_T(t_e2 += clock64() - t1;)
+            }
+            if (it < n_it) {   // epilogue 1 of board it: out[m] = D_a[m] + D_b[m - 1], bias, ReLU, bf16, in place
+                const int ab = it & 1;
+                const uint32_t par = (it >> 1) & 1;
+                GN_T(long long t0 = clock64();)
+                ptx::mbar_wait(&d1_full[ab], par);
+                GN_T(long long t1 = clock64(); w_d1f += t1 - t0;)
+                ptx::mbar_wait(&mid_empty[ab], par ^ 1);
+                GN_T(long long t2 = clock64(); w_me += t2 - t1;)
+                ptx::tc_fence_after();
+                const uint32_t td1 = tlane + ab * 256;
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float va[16], vb[16];
+                    tmem_ld16x2(td1 + c0, td1 + 64 + c0, va, vb);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        float up = __shfl_up_sync(0xffffffffu, vb[i], 1);
+                        if (lane == 0) up = 0.f;     // board column 0: the row above in the tile is the zero padding column
+                        va[i] = fmaxf(va[i] + up + kc.b3[c0 + i], 0.f);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = ptx::pack_bf16(va[2 * i], va[2 * i + 1]);
+                    ptx::tmem_st8(td1 + c0 / 2, pk);
+                }
+                ptx::tmem_wait_st();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
+                GN_T(t_e1 += clock64() - t2;)
+            }
+        }
+        GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 2 || warp == 9) && n_it > 0)
+                 printf("gn(pairs) epilogue warp %d: per board: wait d1_full %lld, mid_empty %lld, epi1 %lld, wait d2_full %lld, epi2 %lld\n",
+                        warp, w_d1f / n_it, w_me / n_it, t_e1 / n_it, w_d2f / n_it, t_e2 / n_it);)
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *out, uint8_t *head_out, int G,
+                            cudaStream_t s) {
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(k_gn_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
         cudaFuncSetAttribute(k_gn_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
+        cudaFuncSetAttribute(k_gn_block_pairs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg::SMEM);
+        cudaFuncSetAttribute(k_gn_block_pairs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg::SMEM);
         configured = true;
     }
     GnBlockConsts kc;
     memcpy(kc.b3, e.bw.gn_host_bias[block], sizeof(float) * 128);   // b3 then b1
     memcpy(kc.head_w, e.bw.gn_host_head, sizeof(float) * 130);       // head_w then head_b
+    const uint8_t *w1 = e.bw.gn_l1_w[block];
     int grid = G < e.sm_count ? G : e.sm_count;
-    if (head_out) k_gn_block<true><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
-    else k_gn_block<false><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
+    static const bool pairs = !(getenv("GZ_GN_PAIRS") && atoi(getenv("GZ_GN_PAIRS")) == 0);   // A/B switch for profiling
+    if (pairs) {
+        const uint8_t *w3 = e.bw.gn_l3p_w[block];
+        if (head_out) k_gn_block_pairs<true><<<grid, 352, GnPairsCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
+        else k_gn_block_pairs<false><<<grid, 352, GnPairsCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
+    } else {
+        const uint8_t *w3 = e.bw.gn_l3_w[block];
+        if (head_out) k_gn_block<true><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
+        else k_gn_block<false><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
+    }
 }
 
 // ---- host side -------------------------------------------------------------------------------------
@@ -680,8 +994,7 @@ void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *ac
     launch_conv<16, 64, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.gn_embed_w,
                                               e.gn.embed.b, nullptr, p0, active, G, s);
     for (int i = 0; i < 4; ++i) {   // p0 -> p1 -> p0 -> p1 -> p0
-        launch_gn_block(e, (i & 1) ? p1 : p0, w.gn_l3_w[i], w.gn_l1_w[i], i,
-                        (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s);
+        launch_gn_block(e, (i & 1) ? p1 : p0, i, (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s);
     }
     prof_end(e, s);
 }

@@ -10,7 +10,7 @@ stale fixture cannot go unnoticed.
 Parts (each -> tests/golden/oracle_<part>.npz):
   config3  BASELINE config 3 (hard preset as the README quotes it: S=200, c_puct 1.8, beta 0.2, planner_steps 5,
            k 16, alpha 0.75, explore 0.05), Philox randomness shared with the engine (key = SEED, counter =
-           (step, simulation, game id, tag)): 128 of the 4096 workload positions (every 32nd, all stone counts),
+           (step, simulation, game id, tag)): 132 of the 4096 workload positions (every 31st: all six stone counts),
            game ids GAME_BASE + k.  Whole trees + the near-tie diagnostics of the blended pick.
   gaps     near-tie diagnostics (min top-2 gap of the blended pick) of the DET-B reference trees in
            mcts_planner.npz, for the bf16 flip accounting.
@@ -35,7 +35,7 @@ import oracle as orc  # noqa: E402
 from weights import make_state_dict  # noqa: E402
 
 # config 3 (shared with tests/test_gpu_timed_path.py)
-C3 = dict(G=4096, workload_seed=3, stride=32, first=7, S=200, c_puct=1.8, beta=0.2, planner_steps=5,
+C3 = dict(G=4096, workload_seed=3, stride=31, first=7, S=200, c_puct=1.8, beta=0.2, planner_steps=5,
           difficulty="hard", seed=0xB200C0DE, game_base=5000)
 STOCH = dict(n=102400, chunk=2048, seed=0x0AC1E5EED, game_base=0)
 
@@ -114,7 +114,9 @@ def part_gaps(pool, outdir):
 def _stoch_task(args):
     pos, cells, tm, mc, ps, lo, hi = args
     O = _oracle()
-    O.L.gzo_set_planner_cache(1 << 14)
+    if not getattr(O, '_cache_on', False):
+        O.L.gzo_set_planner_cache(1 << 15)
+        O._cache_on = True
     b = orc.board_from_cells(cells, tm, mc)
     p = O.params(1, 1.8, 0.2, ps, tm, "hard")
     counts = np.zeros(4, np.int64)
