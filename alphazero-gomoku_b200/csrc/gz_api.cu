@@ -541,6 +541,21 @@ extern "C" int gz_pv_forward(gz_handle h, const gz_board *d_boards, int32_t G, f
     return GZ_OK;
 }
 
+extern "C" int gz_pv_forward_static(gz_handle h, const gz_board *d_boards, int32_t G, float *d_logits,
+                                    float *d_probs, float *d_value, void *stream) {
+    Engine *e = eng(h);
+    if (!e) return fail(GZ_ERR_ARG, "gz_pv_forward_static: null handle");
+    if (!d_boards) return fail(GZ_ERR_ARG, "gz_pv_forward_static: null pointer");
+    if (G < 1) return fail(GZ_ERR_ARG, "gz_pv_forward_static: G must be at least 1");
+    if (G > GZ_STATIC_MAX_BOARDS)
+        return fail(GZ_ERR_ARG, "gz_pv_forward_static: G exceeds GZ_STATIC_MAX_BOARDS (16): the static scratch holds "
+                                "no more; use gz_pv_forward");
+    if (!e->have_pv) return fail(GZ_ERR_STATE, "gz_pv_forward_static: gz_set_pv_weights was not called");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(nn_pv_forward_static(*e, d_boards, G, d_logits, d_probs, d_value, strm(stream)));
+    return GZ_OK;
+}
+
 extern "C" int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, int32_t G,
                                        float *d_gn_logits, float *d_gn_policy, float *d_dqn_q,
                                        void *stream) {

@@ -258,6 +258,10 @@ void nn_pv_forward_fp32(Engine &e, const gz_board *boards, const uint8_t *active
 void nn_planner_forward_fp32(Engine &e, const gz_board *boards, int G, float *gn_logits,
                              float *gn_policy, int policy_pitch, float *dqn_q, cudaStream_t s);
 
+// allocation-free fp32 policy-value forward on a file-scope device array (gz_nn_fp32.cu; gz_pv_forward_static)
+cudaError_t nn_pv_forward_static(Engine &e, const gz_board *boards, int G, float *logits, float *probs, float *value,
+                                 cudaStream_t s);
+
 // networks, bf16 tcgen05 path (gz_nn_bf16.cu)
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
                         float *logits, float *probs, float *value, float *prior_out,

@@ -353,6 +353,54 @@ void nn_debug_pv_layer_fp32(Engine &e, const gz_board *boards, int G, int nlayer
     cudaMemcpyAsync(out, last, sizeof(float) * (size_t)G * 128 * kCells, cudaMemcpyDeviceToDevice, s);
 }
 
+// ---- gz_pv_forward_static: the policy-value forward without any allocation -----------------------------
+// Activation scratch of the fp32 forward (three ping-pong buffers [G][128][225] f32) in a file-scope device array
+// instead of the handle's cudaMalloc'ed buffers, for callers that must not allocate (CUDA-graph capture, serving
+// loops).  kStaticBytes = 5 529 600 bytes for GZ_STATIC_MAX_BOARDS = 16 boards; every GPU that loads the
+// library holds it until exit.  ONE array per device shared by every handle and every call: it keeps the last call's
+// contents (nothing has to start at zero: every layer writes each element of its output for boards [0, G) before the
+// next layer reads it), and two calls that overlap on the GPU (different streams) race on it.
+constexpr size_t kStaticActFloats = (size_t)GZ_STATIC_MAX_BOARDS * 128 * kCells;
+constexpr size_t kStaticBytes = 3 * kStaticActFloats * sizeof(float);
+static __device__ __align__(256) float g_static_act[3 * kStaticActFloats];
+
+// In host code `g_static_act` is a host-side stand-in for the symbol, not a device address: the address is looked up
+// once per device, with that device current, and cached.
+static float *static_scratch(int device, cudaError_t *err) {
+    constexpr int kMaxDevices = 64;
+    static float *ptr[kMaxDevices];
+    *err = cudaSuccess;
+    if (device < 0 || device >= kMaxDevices) { *err = cudaErrorInvalidDevice; return nullptr; }
+    if (!ptr[device]) {
+        float *p = nullptr;
+        *err = cudaGetSymbolAddress((void **)&p, g_static_act);
+        if (*err != cudaSuccess) return nullptr;
+        ptr[device] = p;
+    }
+    return ptr[device];
+}
+
+// The same six kernels as nn_pv_forward_fp32 (fp32 FFMA, weights of gz_set_pv_weights) on the static scratch.
+// e's device must be current.  No stage events (their pool grows by allocation).
+cudaError_t nn_pv_forward_static(Engine &e, const gz_board *boards, int G, float *logits, float *probs, float *value,
+                                 cudaStream_t s) {
+    cudaError_t err;
+    float *a0 = static_scratch(e.cfg.device, &err);
+    if (!a0) return err;
+    float *a1 = a0 + kStaticActFloats, *a2 = a1 + kStaticActFloats;
+    const PvWeights &w = e.pv;
+    k_conv<3, 128, 3, true, false, true><<<G, 256, 0, s>>>(nullptr, boards, nullptr, w.conv0.w, w.conv0.b, nullptr, a0);
+    k_conv<128, 128, 3, false, false, true><<<G, 256, 0, s>>>(a0, nullptr, nullptr, w.tower[0].w, w.tower[0].b, nullptr, a1);
+    k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, nullptr, w.tower[1].w, w.tower[1].b, a0, a2);
+    k_conv<128, 128, 3, false, false, true><<<G, 256, 0, s>>>(a2, nullptr, nullptr, w.tower[2].w, w.tower[2].b, nullptr, a1);
+    k_conv<128, 128, 3, false, true, true><<<G, 256, 0, s>>>(a1, nullptr, nullptr, w.tower[3].w, w.tower[3].b, a2, a0);
+    k_heads<128, true, false><<<(G + kHeadNB - 1) / kHeadNB, 256, 0, s>>>(
+        a0, boards, nullptr, G, w.pconv_w, w.pconv_b, w.pfc_wt, w.pfc_b, w.vconv_w, w.vconv_b,
+        w.vfc1_wt, w.vfc1_b, w.vfc2_w, w.vfc2_b, logits, probs, value, nullptr, nullptr, 0, nullptr, kCells);
+    e.launches += 6;
+    return cudaGetLastError();
+}
+
 void nn_pv_forward(Engine &e, const gz_board *boards, const uint8_t *active, int G, float *logits,
                    float *probs, float *value, float *prior_out, const int32_t *prior_slot, cudaStream_t s) {
     if (e.cfg.precision == 1) nn_pv_forward_bf16(e, boards, active, G, logits, probs, value, prior_out, prior_slot, s);

@@ -23,8 +23,10 @@ EXPORTS = [
     "gz_rollout_policy", "gz_rollout", "gz_search", "gz_search_host", "gz_get_tree",
     "gz_get_counters", "gz_reset_counters", "gz_set_profiling", "gz_set_lanes", "gz_get_stage_times", "gz_debug_pv_layer",
     "gz_selfplay_begin", "gz_selfplay_step", "gz_selfplay_drain", "gz_selfplay_boards", "gz_selfplay_get_stats",
-    "gz_dataset_build", "gz_arena_begin", "gz_arena_get_stats", "gz_get_priors", "gz_set_graph", "gz_selfplay_set_simulations",
+    "gz_dataset_build", "gz_arena_begin", "gz_arena_get_stats", "gz_get_priors", "gz_set_graph", "gz_selfplay_set_simulations", "gz_pv_forward_static",
 ]
+
+STATIC_MAX_BOARDS = 16    # GZ_STATIC_MAX_BOARDS
 
 ARENA_ENGINE, ARENA_RANDOM = 1, 2     # GZ_ARENA_ENGINE / GZ_ARENA_RANDOM
 
@@ -216,6 +218,14 @@ class Engine:
         self._ck(self.L.gz_pv_forward(self.h, _ptr(boards), G, _ptr(logits), _ptr(probs), _ptr(value),
                                       self._stream()))
         return logits, probs, value
+
+    def pv_forward_static(self, boards, out):
+        """gz_pv_forward_static: at most STATIC_MAX_BOARDS boards, activations in the library's static device array,
+        no allocation inside the call; `out` = caller-owned (logits [G,225], probs [G,225], value [G]) f32 tensors."""
+        logits, probs, value = out
+        self._ck(self.L.gz_pv_forward_static(self.h, _ptr(boards), int(boards.shape[0]), _ptr(logits), _ptr(probs),
+                                             _ptr(value), self._stream()))
+        return out
 
     def debug_pv_layer(self, boards, nlayers):
         G = boards.shape[0]

@@ -157,6 +157,21 @@ int gz_pv_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_log
 int gz_planner_nets_forward(gz_handle h, const gz_board *d_boards, int32_t G, float *d_gn_logits,
                             float *d_gn_policy, float *d_dqn_q, void *stream);
 
+/* gz_pv_forward without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same outputs as gz_pv_forward on a precision-0 handle (the fp32 FFMA kernels, weights of
+ * gz_set_pv_weights; a precision-1 handle also computes in fp32 here), but the activation scratch is a file-scope
+ * `static __device__` array inside the library instead of the handle's buffers: 3 x GZ_STATIC_MAX_BOARDS x 128 x 225
+ * floats = 5 529 600 bytes, held by every GPU that loads the library until exit.  G > GZ_STATIC_MAX_BOARDS is
+ * rejected with GZ_ERR_ARG.  The call performs no cudaMalloc / cudaFree and uses no allocating library routine; the
+ * caller owns inputs and outputs (any output may be NULL).  The array is shared by all handles and calls on a device
+ * and keeps the last call's contents (nothing needs clearing: each layer overwrites what the next one reads); calls
+ * that overlap on the GPU (different streams) race on it -- serialise them.  The array's device address is looked up
+ * on the first call per device: make that call outside a graph capture. */
+#define GZ_STATIC_MAX_BOARDS 16
+int gz_pv_forward_static(gz_handle h, const gz_board *d_boards, int32_t G, float *d_logits, float *d_probs,
+                         float *d_value, void *stream);
+
 /* Inspection: output of the input convolution (nlayers = 0) or of the first nlayers (1..4) tower
  * convolutions of AlphaZeroGomokuNet in the handle's precision, as fp32 NCHW d_out f32[G,128,225]
  * (neural_network.py:142-146, :85-91).  Used by the per-layer parity tests. */
