@@ -1,6 +1,6 @@
 """Per-kernel counts of the Blackwell-only SASS opcodes in libgomoku_b200.so (cuobjdump -sass):
 UTCHMMA = tcgen05.mma, LDTM / STTM = tcgen05.ld / tcgen05.st, UTCBAR = tcgen05.commit, UBLKCP = cp.async.bulk,
-UTCATOMSWS / UTCALLOC-family = tensor-memory allocation, SYNCS = mbarrier ops.  usage: sass_opcodes.py [lib.so] > table.md"""
+UTCATOMSWS = tensor-memory allocation, SYNCS = mbarrier ops.  usage: sass_opcodes.py [lib.so] > table.md"""
 import collections
 import re
 import subprocess
@@ -27,8 +27,8 @@ for line in out.splitlines():
                 counts[cur][pat] += 1
         counts[cur]["_all"] += 1
 demangle = subprocess.run(["c++filt"] + list(counts), capture_output=True, text=True).stdout.splitlines()
-print("| kernel | instructions | " + " | ".join(OPS) + " |")
+print("| kernel | instructions | " + " | ".join(o.replace("|", "/") for o in OPS) + " |")
 print("|---|---|" + "---|" * len(OPS))
 for (name, c), dm in sorted(zip(counts.items(), demangle), key=lambda x: -x[0][1]["UTCHMMA"]):
-    short = re.sub(r"\(.*", "", dm).replace("void gz::", "")
+    short = re.sub(r"\(.*", "", dm).replace("void gz::", "").replace("gz::", "")
     print("| `%s` | %d | " % (short[:70], c["_all"]) + " | ".join(str(c[p]) if c[p] else "" for p in OPS) + " |")
