@@ -19,3 +19,21 @@ head, units, vals = rows[0], rows[1], rows[2]
 for n, u, v in zip(head, units, vals):
     if n == "Kernel Name": print(n, "=", v[:110])
     if n in WANT: print(f"{n} = {v} {u}")
+
+# `--traffic STAGE`: record dram bytes read + written per launch of this kernel in profiles/ncu_traffic.json, the file
+# bench.py's roofline.traffic is read from (stage names = bench.py's stage_ms keys)
+if "--traffic" in sys.argv:
+    import json, os
+    stage = sys.argv[sys.argv.index("--traffic") + 1]
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    rec = dict(zip(head, zip(units, vals)))
+    tot = sum(float(rec[m][1].replace(",", "")) * scale[rec[m][0]] for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_traffic.json")
+    try:
+        d = json.load(open(path))
+    except Exception:
+        d = {}
+    d[stage] = {"bytes_per_launch": tot, "kernel": rec["Kernel Name"][1][:60], "capture": os.path.basename(sys.argv[1]),
+                "us": rec["gpu__time_duration.sum"][1]}
+    json.dump(d, open(path, "w"), indent=1)
+    print("wrote", path, d[stage])
