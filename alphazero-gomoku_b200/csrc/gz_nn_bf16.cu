@@ -654,11 +654,12 @@ k_gn_block(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3
 // that every pair UMMA accumulates (the first single of a board initialises D_a alone: a pair cannot initialise one
 // half of its 128 columns and accumulate into the other).  Singles are issued first, which gives epilogue 2 of the
 // board two back the time it needs before the pairs touch D_b.
+template <int NSLAB>
 struct GnPairsCfg {
     static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
     static constexpr int PAIR_BYTES = 8 * 128 * 16, SINGLE_BYTES = 8 * 64 * 16;
     static constexpr int W3_BYTES = 3 * PAIR_BYTES + 3 * SINGLE_BYTES, W1_BYTES = 8 * 64 * 16;
-    static constexpr int SMEM = 2 * SLAB_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
+    static constexpr int SMEM = NSLAB * SLAB_BYTES + W3_BYTES + W1_BYTES + 2 * 64 * 4 + 256 + 132 * 4;
 };
 
 // two x16 loads in flight, one wait
@@ -686,26 +687,30 @@ __device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, float *va,
     for (int i = 0; i < 16; ++i) { va[i] = __uint_as_float(a[i]); vb[i] = __uint_as_float(b[i]); }
 }
 
-template <bool FINAL>
+// NSLAB input slab buffers (the loads come from HBM: with two, the issuers waited 200-460 cycles per board for a_full).
+// rev: boards are walked from the last to the first.  Consecutive layers alternate the direction, so a layer starts on
+// the boards its predecessor wrote last -- the part of the 151 MB plane buffer that is still in the 126 MB L2.
+template <bool FINAL, int NSLAB>
 __global__ void __launch_bounds__(352, 1)
 k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
                  const __grid_constant__ GnBlockConsts kc, uint8_t *__restrict__ out_planes,
-                 uint8_t *__restrict__ head_out, int G) {
-    using C = GnPairsCfg;
+                 uint8_t *__restrict__ head_out, int G, int rev) {
+    using C = GnPairsCfg<NSLAB>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *slab = smem;
-    uint8_t *sw3 = slab + 2 * C::SLAB_BYTES;      // [3 pair blocks: 8 cg x 128 rows x 16 B][3 single blocks: 8 cg x 64 x 16 B]
+    uint8_t *sw3 = slab + NSLAB * C::SLAB_BYTES;      // [3 pair blocks: 8 cg x 128 rows x 16 B][3 single blocks: 8 cg x 64 x 16 B]
     uint8_t *sw1 = sw3 + C::W3_BYTES;
     uint64_t *bars = reinterpret_cast<uint64_t *>(sw1 + C::W1_BYTES + 2 * 64 * 4);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *d1_full = bars + 4, *d1_empty = bars + 6;
-    uint64_t *mid_full = bars + 8, *mid_empty = bars + 10, *d2_full = bars + 12, *d2_empty = bars + 14;
-    uint64_t *w_full = bars + 16;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 17);
+    static_assert(NSLAB >= 2 && NSLAB <= 4, "slab ring");
+    uint64_t *a_full = bars, *a_empty = bars + 4, *d1_full = bars + 8, *d1_empty = bars + 10;
+    uint64_t *mid_full = bars + 12, *mid_empty = bars + 14, *d2_full = bars + 16, *d2_empty = bars + 18;
+    uint64_t *w_full = bars + 20;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 21);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
     if (threadIdx.x == 0) {
+        for (int i = 0; i < NSLAB; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 2); }
         for (int i = 0; i < 2; ++i) {   // every tcgen05.commit comes twice: one per issuer warp (M half)
-            ptx::mbar_init(&a_full[i], 1);   ptx::mbar_init(&a_empty[i], 2);
             ptx::mbar_init(&d1_full[i], 2);  ptx::mbar_init(&d1_empty[i], 8);
             ptx::mbar_init(&mid_full[i], 8); ptx::mbar_init(&mid_empty[i], 2);
             ptx::mbar_init(&d2_full[i], 2);  ptx::mbar_init(&d2_empty[i], 8);
@@ -721,6 +726,7 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
     const int n_it = blockIdx.x < G ? (G - 1 - blockIdx.x) / gridDim.x + 1 : 0;
     // accumulator block of (buffer ab, M half h): 128 columns [D_a | D_b]
     auto acc_of = [&](int ab, int h) { return tmem_base + (uint32_t)(ab * 256 + h * 128); };
+    auto board_of = [&](int it) { const int b = blockIdx.x + it * (int)gridDim.x; return rev ? G - 1 - b : b; };
 
     if (warp == 0) {
         if (lane == 0) {
@@ -728,8 +734,8 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
             for (int t = 0; t < 9; ++t) ptx::bulk_g2s(sw3 + t * 8192, w3 + t * 8192, 8192, w_full);
             ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
             for (int it = 0; it < n_it; ++it) {
-                const int b = blockIdx.x + it * gridDim.x, ab = it & 1;
-                ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+                const int b = board_of(it), ab = it % NSLAB;
+                ptx::mbar_wait(&a_empty[ab], ((it / NSLAB) & 1) ^ 1);
                 ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
                 const uint8_t *src = in_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes - 16;
                 for (int cg = 0; cg < 8; ++cg)
@@ -753,7 +759,7 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
             GN_T(long long t0 = clock64();)
             ptx::mbar_wait(&d1_empty[ab], par ^ 1);
             GN_T(long long t1 = clock64(); w_d1e += t1 - t0;)
-            ptx::mbar_wait(&a_full[ab], par);
+            ptx::mbar_wait(&a_full[it % NSLAB], (it / NSLAB) & 1);
             GN_T(w_af += clock64() - t1;)
             ptx::tc_fence_after();
         };
@@ -775,7 +781,7 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
         for (int it = 0; it < n_it; ++it) {
             const int ab = it & 1;
             GN_T(long long t2 = clock64();)
-            const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
+            const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + (it % NSLAB) * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
             const uint32_t acc = acc_of(ab, h);
             // singles first: the dx = +1 taps, N = 64 into D_a; the very first one initialises D_a
 #pragma unroll
@@ -806,7 +812,7 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
             if (it + 1 < n_it) wait_board(it + 1);
             GZ_GN_PAIR(2, 2, 4)
 #undef GZ_GN_PAIR
-            ptx::umma_commit_elect(&a_empty[ab]);
+            ptx::umma_commit_elect(&a_empty[it % NSLAB]);
             ptx::umma_commit_elect(&d1_full[ab]);
             GN_T(t_i3 += clock64() - t2;)
         }
@@ -834,7 +840,7 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
         for (int it = 0; it <= n_it; ++it) {
             if (it > 0) {   // epilogue 2 of board it - 1 (its 1x1 ran in the middle of board it's 3x3)
                 const int j = it - 1, jb = j & 1;
-                const int b = blockIdx.x + j * gridDim.x;
+                const int b = board_of(j);
                 GN_T(long long t0 = clock64();)
                 ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
                 GN_T(long long t1 = clock64(); w_d2f += t1 - t0;)
@@ -929,8 +935,10 @@ static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *ou
     if (!configured) {
         cudaFuncSetAttribute(k_gn_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
         cudaFuncSetAttribute(k_gn_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
-        cudaFuncSetAttribute(k_gn_block_pairs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg::SMEM);
-        cudaFuncSetAttribute(k_gn_block_pairs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg::SMEM);
+        cudaFuncSetAttribute(k_gn_block_pairs<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg<2>::SMEM);
+        cudaFuncSetAttribute(k_gn_block_pairs<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg<2>::SMEM);
+        cudaFuncSetAttribute(k_gn_block_pairs<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg<3>::SMEM);
+        cudaFuncSetAttribute(k_gn_block_pairs<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg<3>::SMEM);
         configured = true;
     }
     GnBlockConsts kc;
@@ -939,10 +947,18 @@ static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *ou
     const uint8_t *w1 = e.bw.gn_l1_w[block];
     int grid = G < e.sm_count ? G : e.sm_count;
     static const bool pairs = !(getenv("GZ_GN_PAIRS") && atoi(getenv("GZ_GN_PAIRS")) == 0);   // A/B switch for profiling
+    static const int nslab = getenv("GZ_GN_SLABS") ? atoi(getenv("GZ_GN_SLABS")) : 3;                // A/B switches
+    static const bool alternate = !(getenv("GZ_GN_ALTERNATE") && atoi(getenv("GZ_GN_ALTERNATE")) == 0);
+    const int rev = alternate ? (block & 1) ^ 1 : 0;   // the embed writes ascending: block 0 walks back, block 1 forth, ...
     if (pairs) {
         const uint8_t *w3 = e.bw.gn_l3p_w[block];
-        if (head_out) k_gn_block_pairs<true><<<grid, 352, GnPairsCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
-        else k_gn_block_pairs<false><<<grid, 352, GnPairsCfg::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G);
+        if (nslab == 3) {
+            if (head_out) k_gn_block_pairs<true, 3><<<grid, 352, GnPairsCfg<3>::SMEM, s>>>(in, w3, w1, kc, out, head_out, G, rev);
+            else k_gn_block_pairs<false, 3><<<grid, 352, GnPairsCfg<3>::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G, rev);
+        } else {
+            if (head_out) k_gn_block_pairs<true, 2><<<grid, 352, GnPairsCfg<2>::SMEM, s>>>(in, w3, w1, kc, out, head_out, G, rev);
+            else k_gn_block_pairs<false, 2><<<grid, 352, GnPairsCfg<2>::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G, rev);
+        }
     } else {
         const uint8_t *w3 = e.bw.gn_l3_w[block];
         if (head_out) k_gn_block<true><<<grid, 352, GnBlockCfg::SMEM, s>>>(in, w3, w1, kc, out, head_out, G);
