@@ -72,7 +72,7 @@ template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_B
 __global__ void __launch_bounds__(64 + 32 * conv_epi_warps<FROM_BOARD>(), 1)
 k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w_packed,
             const float *__restrict__ bias, const uint8_t *__restrict__ res_planes,
-            uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G, HeadConv heads) {
+            uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G, HeadConv heads, int rev) {
     using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *slab = smem;                                   // [2][SLAB_BYTES]
@@ -85,6 +85,9 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
     float *s_hw = reinterpret_cast<float *>(bars + 32);     // HEADS: [COUT][2] policy, [COUT] value, 3 biases
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
+    // rev: the loop index b walks the boards from the last to the first (memory index ph(b)); consecutive layers
+    // alternate, so a layer starts on the boards its predecessor wrote last, the ones still in L2
+    auto ph = [&](int b) { return rev ? G - 1 - b : b; };
     if (HEADS) {
         for (int i = threadIdx.x; i < 2 * COUT; i += blockDim.x) s_hw[i] = heads.pw[i];
         for (int i = threadIdx.x; i < COUT; i += blockDim.x) s_hw[2 * COUT + i] = heads.vw[i];
@@ -125,12 +128,12 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
         // the next board's bitboards are fetched while this one is expanded (the loop is otherwise one global
         // load latency per board long)
         auto next_board = [&](int b) {
-            for (b += gridDim.x; b < G && active && !active[b]; b += gridDim.x) {}
+            for (b += gridDim.x; b < G && active && !active[ph(b)]; b += gridDim.x) {}
             return b;
         };
-        auto load_stones = [&](int b) { return lane < 16 && b < G ? boards[b].stones[lane >> 3][lane & 7] : 0u; };
+        auto load_stones = [&](int b) { return lane < 16 && b < G ? boards[ph(b)].stones[lane >> 3][lane & 7] : 0u; };
         uint32_t it = 0;
-        int b = blockIdx.x < G && active && !active[blockIdx.x] ? next_board(blockIdx.x) : blockIdx.x;
+        int b = blockIdx.x < G && active && !active[ph(blockIdx.x)] ? next_board(blockIdx.x) : blockIdx.x;
         uint32_t st = load_stones(b);
         while (b < G) {
             const int ab = it & 1;
@@ -169,11 +172,11 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             }
             uint32_t it = 0, wstage = 0, wphase = 0;
             for (int b = blockIdx.x; b < G; b += gridDim.x) {
-                if (active && !active[b]) continue;
+                if (active && !active[ph(b)]) continue;
                 const int ab = it & 1;
                 ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
                 ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
-                const uint8_t *src = in_planes + kGuardBytes + (size_t)b * C::CG * kPlaneBytes +
+                const uint8_t *src = in_planes + kGuardBytes + (size_t)ph(b) * C::CG * kPlaneBytes +
                                      (TAPS == 9 ? -16 : 256);
                 for (int cg = 0; cg < C::CG; ++cg)
                     ptx::bulk_g2s(slab + ab * C::SLAB_BYTES + cg * C::SLAB_ROWS * 16,
@@ -198,7 +201,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             if (RESIDENT) ptx::mbar_wait(&b_full[0], 0);
             uint32_t it = 0, wstage = 0, wphase = 0;
             for (int b = blockIdx.x; b < G; b += gridDim.x) {
-                if (active && !active[b]) continue;
+                if (active && !active[ph(b)]) continue;
                 const int ab = it & 1;
                 const uint32_t par = (it >> 1) & 1;
                 ptx::mbar_wait(&acc_empty[ab], par ^ 1);
@@ -247,13 +250,15 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
         const int q = warp & 3;                 // TMEM lane quadrant this warp may read
         constexpr int NCG = COUT / 8;
         uint4 res[2][RESIDUAL ? NCG : 1];
-        auto fetch_res = [&](int b, int h, uint4 *r) {
+        auto fetch_res = [&](int bl, int h, uint4 *r) {
+            const int b = ph(bl);
             const uint8_t *src = res_planes + kGuardBytes + (size_t)b * NCG * kPlaneBytes +
                                  (size_t)(16 + 128 * h + 32 * q + lane) * 16;
 #pragma unroll
             for (int cg = 0; cg < NCG; ++cg) r[cg] = *reinterpret_cast<const uint4 *>(src + (size_t)cg * kPlaneBytes);
         };
-        auto half = [&](int b, int ab, int h, const uint4 *r) {
+        auto half = [&](int bl, int ab, int h, const uint4 *r) {
+            const int b = ph(bl);
             const size_t obase = kGuardBytes + (size_t)b * NCG * kPlaneBytes;
             const int pos = 16 + 128 * h + 32 * q + lane;
             const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
@@ -323,11 +328,11 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             }
         };
         auto next_board = [&](int b) {
-            for (b += gridDim.x; b < G && active && !active[b]; b += gridDim.x) {}
+            for (b += gridDim.x; b < G && active && !active[ph(b)]; b += gridDim.x) {}
             return b;
         };
         uint32_t it = 0;
-        int b = blockIdx.x < G && active && !active[blockIdx.x] ? next_board(blockIdx.x) : blockIdx.x;
+        int b = blockIdx.x < G && active && !active[ph(blockIdx.x)] ? next_board(blockIdx.x) : blockIdx.x;
         if (RESIDUAL && b < G) fetch_res(b, 0, res[0]);
         while (b < G) {
             const int ab = it & 1;
@@ -970,7 +975,7 @@ static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *ou
 template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false, bool HEADS = false>
 static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const float *bias,
                         const uint8_t *res, uint8_t *out, const uint8_t *active, int G, cudaStream_t s,
-                        HeadConv heads = HeadConv()) {
+                        HeadConv heads = HeadConv(), int rev = 0) {
     using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
     auto kern = k_conv_umma<CIN, COUT, TAPS, RESIDENT, RESIDUAL, FROM_BOARD, HEADS>;
     static bool configured = false;
@@ -981,7 +986,9 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
     int grid = G < e.sm_count ? G : e.sm_count;
     static const int cap = getenv("GZ_CONV_GRID") ? atoi(getenv("GZ_CONV_GRID")) : 0;   // EXPERIMENT
     if (cap > 0 && grid > cap) grid = cap;
-    kern<<<grid, 64 + 32 * conv_epi_warps<FROM_BOARD>(), C::SMEM, s>>>(in, w, bias, res, out, active, G, heads);
+    static const bool alternate = !(getenv("GZ_GN_ALTERNATE") && atoi(getenv("GZ_GN_ALTERNATE")) == 0);   // A/B switch
+    kern<<<grid, 64 + 32 * conv_epi_warps<FROM_BOARD>(), C::SMEM, s>>>(in, w, bias, res, out, active, G, heads,
+                                                                       alternate ? rev : 0);
 }
 
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
@@ -994,11 +1001,12 @@ void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active
                                                e.pv.conv0.b, nullptr, p0, active, G, s);
     prof_end(e, s);
     prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
-    launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s);
-    launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s);
-    launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s);
+    // board direction alternates layer by layer (the input convolution walks forward): see k_conv_umma's `rev`
+    launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s, HeadConv(), 1);
+    launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s, HeadConv(), 0);
+    launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s, HeadConv(), 1);
     HeadConv hc = {e.pv.pconv_w, e.pv.pconv_b, e.pv.vconv_w, e.pv.vconv_b, e.pv_pc, e.pv_vc};
-    launch_conv<128, 128, 9, false, true, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s, hc);
+    launch_conv<128, 128, 9, false, true, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s, hc, 0);
     prof_end(e, s);
     nn_heads_bf16(e, true, boards, active, G, nullptr, logits, probs, value, prior_out, prior_slot, s);
 }
