@@ -32,21 +32,43 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
     BB empty = bb_empty_cells(black, white);
     const int a = ai_player[g];
     const BB o_st = (a == 1) ? white : black;
-    // line words of both colours and the per-line pattern score of A (gz_lines.cuh)
-    __shared__ uint32_t s_st[4][2][8];
-    __shared__ uint16_t s_la[4][kNumLines], s_lb[4][kNumLines];
+    // Line words by ballot: lane r holds row r of A, lane 16 + r row r of B (lanes 15 and 31 hold nothing), so ONE vote
+    // per line returns A's stones in the low half and B's in the high half, bit = board row; a constant shift turns the
+    // row into the position on the line.  73 votes per board (columns and both diagonal families; a row is the lane's own
+    // word) instead of a 15-step bit gather per line, colour and lane: that loop was 16 % of the kernel's instructions.
+    __shared__ uint32_t s_lab[4][kNumLines];
     __shared__ int32_t s_ls[4][kNumLines];
     const int wi = threadIdx.x >> 5;
-    if (lane < 16) s_st[wi][lane >> 3][lane & 7] = b.stones[(lane >> 3) ^ (a == 1 ? 0 : 1)][lane & 7];
+    const int rr = lane & 15;
+    const uint32_t myrow = (boards[g].stones[(lane >> 4) ^ (a == 1 ? 0 : 1)][rr >> 1] >> ((rr & 1) * 16)) & 0x7FFFu;   // row 15 is empty
+    {
+        const uint32_t other = __shfl_xor_sync(0xffffffffu, myrow, 16);
+        if (lane < 15) s_lab[wi][lane] = myrow | (other << 16);                         // rows: lines 0-14
+#pragma unroll
+        for (int c = 0; c < 15; ++c) {                                                  // columns: lines 15-29
+            const uint32_t w = __ballot_sync(0xffffffffu, (myrow >> c) & 1u);
+            if (lane == 0) s_lab[wi][15 + c] = w;
+        }
+#pragma unroll
+        for (int k = -14; k <= 14; ++k) {                                               // diagonals r - c = k: lines 30-58
+            const int sh = rr - k;
+            const uint32_t w = __ballot_sync(0xffffffffu, sh >= 0 && ((myrow >> sh) & 1u));
+            if (lane == 0) s_lab[wi][44 + k] = w >> (k > 0 ? k : 0);
+        }
+#pragma unroll
+        for (int d = 0; d <= 28; ++d) {                                                 // anti-diagonals r + c = d: lines 59-87
+            const int sh = d - rr;
+            const uint32_t w = __ballot_sync(0xffffffffu, sh >= 0 && ((myrow >> sh) & 1u));
+            if (lane == 0) s_lab[wi][59 + d] = w >> (d > 14 ? d - 14 : 0);
+        }
+    }
     __syncwarp();
     int ls_sum = 0;
     for (int i = lane; i < kNumLines; i += 32) {
         int r0, c0, len;
         line_cell(i, 0, r0, c0, len);
-        uint32_t xa = line_word(s_st[wi][0], i), xb = line_word(s_st[wi][1], i);
+        const uint32_t w = s_lab[wi][i], xa = w & 0xFFFFu, xb = w >> 16;
         int32_t v = line_score(xa, ((1u << len) - 1u) & ~(xa | xb));
-        s_la[wi][i] = (uint16_t)xa;
-        s_lb[wi][i] = (uint16_t)xb;
         s_ls[wi][i] = v;
         ls_sum += v;
     }
@@ -81,7 +103,7 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
         if (32 * i < n_e) {                      // warp-uniform: whole rounds past the list are skipped
             if (r < n_e) {
                 const int pp = s_cell[wi][r];
-                const long long sc = planner_score2_lines(s_la[wi], s_lb[wi], s_ls[wi], s_a, n_win_b,
+                const long long sc = planner_score2_lines(s_lab[wi], s_ls[wi], s_a, n_win_b,
                                                           (s_win[wi][pp >> 5] >> (pp & 31)) & 1u, b.to_move, a,
                                                           b.move_count, pp);
                 key[i] = (uint32_t)(sc + (1ll << 30));

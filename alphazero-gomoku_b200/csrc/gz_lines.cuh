@@ -104,25 +104,35 @@ GZ_HD uint32_t line_win_cells(uint32_t X, uint32_t E) {
 }
 
 // Planner candidate score (planner_score2 in gz_policy.cuh, same contract) from the line words.
-//   la, lb      : line words of the planner's colour A and of the other colour B   [88]
+//   lab         : line words of the planner's colour A (low half) and of the other colour B (high half)   [88]
 //   ls_old      : line_score(la[i], empties of line i)                            [88]
 //   s_a         : sum of ls_old = pattern_score(board, A)
 //   n_win_b     : number of empty cells that complete five for B on the board
 //   p_wins_b    : p is one of them
-GZ_HD int64_t planner_score2_lines(const uint16_t *la, const uint16_t *lb, const int32_t *ls_old,
+GZ_HD int64_t planner_score2_lines(const uint32_t *lab, const int32_t *ls_old,
                                    int64_t s_a, int n_win_b, bool p_wins_b, int mover, int a,
                                    int move_count, int p) {
     const int r = p >> 4, c = p & 15;
     const bool mover_is_a = mover == a;
     bool won = false, new_b_win = false;
     int32_t delta = 0;
+    // Two directions per 32-bit word (a line is at most 15 cells: bit 15 of each half is neither a stone nor empty).
+    // Every pattern test of line_score / line_has_five / line_win_cells is an AND over a contiguous run of cells, so no
+    // match can straddle the separator bit, and what a shift carries across it is cleared by the other factors; the
+    // popcounts then add the two lines' scores, which is all the caller needs (the sum over the four directions).
 #pragma unroll
-    for (int dir = 0; dir < 4; ++dir) {
-        int idx, pos, len;
-        line_of(dir, r, c, idx, pos, len);
-        uint32_t xa = la[idx], xb = lb[idx];
-        const uint32_t bit = 1u << pos;
-        uint32_t e2 = ((1u << len) - 1u) & ~(xa | xb) & ~bit;
+    for (int dir = 0; dir < 4; dir += 2) {
+        int i0, p0, l0, i1, p1, l1;
+        line_of(dir, r, c, i0, p0, l0);
+        line_of(dir + 1, r, c, i1, p1, l1);
+        const uint32_t w0 = lab[i0], w1 = lab[i1];
+#ifdef __CUDA_ARCH__
+        uint32_t xa = __byte_perm(w0, w1, 0x5410), xb = __byte_perm(w0, w1, 0x7632);
+#else
+        uint32_t xa = (w0 & 0xFFFFu) | (w1 << 16), xb = (w0 >> 16) | (w1 & 0xFFFF0000u);
+#endif
+        const uint32_t bit = (1u << p0) | (0x10000u << p1);
+        const uint32_t e2 = (((1u << l0) - 1u) | (((1u << l1) - 1u) << 16)) & ~(xa | xb | bit);
         if (mover_is_a) {
             xa |= bit;
             won = won || line_has_five(xa);
@@ -131,7 +141,7 @@ GZ_HD int64_t planner_score2_lines(const uint16_t *la, const uint16_t *lb, const
             won = won || line_has_five(xb);
             new_b_win = new_b_win || line_win_cells(xb, e2) != 0u;
         }
-        delta += line_score(xa, e2) - ls_old[idx];
+        delta += line_score(xa, e2) - ls_old[i0] - ls_old[i1];
     }
     if (won && mover_is_a) return kScoreWin2;
     bool opp_wins;

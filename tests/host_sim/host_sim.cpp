@@ -114,15 +114,15 @@ void hs_planner_scores2_lines(const uint8_t *cells, int to_move, int move_count,
     BB e = bb_empty_cells(bl, wh);
     const BB &a_st = ai == 1 ? bl : wh;
     const BB &o_st = ai == 1 ? wh : bl;
-    uint16_t la[kNumLines], lb[kNumLines];
+    uint32_t lab[kNumLines];
     int32_t ls[kNumLines];
     int64_t s_a = 0;
     for (int i = 0; i < kNumLines; ++i) {
         int r, c, len;
         line_cell(i, 0, r, c, len);
-        la[i] = (uint16_t)line_word(a_st.w, i);
-        lb[i] = (uint16_t)line_word(o_st.w, i);
-        ls[i] = line_score(la[i], ((1u << len) - 1u) & ~(uint32_t)(la[i] | lb[i]));
+        const uint32_t xa = line_word(a_st.w, i), xb = line_word(o_st.w, i);
+        lab[i] = xa | (xb << 16);
+        ls[i] = line_score(xa, ((1u << len) - 1u) & ~(xa | xb));
         s_a += ls[i];
     }
     BB wb, tb;
@@ -130,7 +130,7 @@ void hs_planner_scores2_lines(const uint8_t *cells, int to_move, int move_count,
     int nwb = bb_count(wb);
     for (int i = 0; i < 225; ++i) {
         int p = cell_to_bit(i);
-        scores225[i] = bb_test(e, p) ? planner_score2_lines(la, lb, ls, s_a, nwb, bb_test(wb, p), b.to_move,
+        scores225[i] = bb_test(e, p) ? planner_score2_lines(lab, ls, s_a, nwb, bb_test(wb, p), b.to_move,
                                                             ai, b.move_count, p)
                                      : INT64_MIN;
     }
