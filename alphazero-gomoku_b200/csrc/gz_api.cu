@@ -239,6 +239,15 @@ static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const fl
                     f2bf((float)((double)w[((size_t)co * 3 + ci) * 9 + tap] * scale));
         }
 }
+// GraphNet embed [64][3][3][3] as one im2col GEMM operand for k_gn_block0_embed: K = 27 (k = 3 * tap + plane, plane =
+// black / white / empty) padded to 32 -> [4 k-groups][64 cout][8 k] bf16
+static void pack_embed_im2col_bf16(std::vector<uint16_t> &out, const float *w) {
+    size_t base = out.size();
+    out.resize(base + (size_t)4 * 64 * 8, 0);
+    for (int k = 0; k < 27; ++k)
+        for (int co = 0; co < 64; ++co)
+            out[base + ((size_t)(k >> 3) * 64 + co) * 8 + (k & 7)] = f2bf(w[((size_t)co * 3 + k % 3) * 9 + k / 3]);
+}
 // linear weight [nout][nin] -> K-chunks of 64 inputs: [chunk][8 k-groups][256 n][8 k] bf16, zero padded
 static void pack_fc_bf16(std::vector<uint16_t> &out, const float *w, int nout, int nin, int chunks, int npad = 256) {
     size_t base = out.size();
@@ -389,8 +398,12 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         }
         size_t off0 = bf.size() * 2;
         pack_conv0_bf16(bf, gnf, nullptr, 64);
+        size_t off_i2c = bf.size() * 2;
+        pack_embed_im2col_bf16(bf, gnf);
+        memcpy(e->bw.gn_host_embed_bias, &pk.host[o[1]], 64 * sizeof(float));
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.gn_blob);
         if (rc) return rc;
+        e->bw.gn_embed_i2c_w = e->bw.gn_blob + off_i2c;
         for (int i = 0; i < 4; ++i) {
             e->bw.gn_l3_w[i] = e->bw.gn_blob + o3[i]; e->bw.gn_l1_w[i] = e->bw.gn_blob + o1[i];
             e->bw.gn_l3p_w[i] = e->bw.gn_blob + o3p[i];

@@ -20,6 +20,7 @@
 //             bf16, 16-byte coalesced stores
 #include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 #include "gz_engine.h"
 #include "gz_tcgen05.cuh"
 
@@ -403,6 +404,7 @@ struct GnBlockCfg {
 struct GnBlockConsts {
     float b3[64], b1[64];
     float head_w[128], head_b[2];   // FINAL only: [64][2], [2]
+    float be[64];                   // k_gn_block0_embed only: the embed convolution's bias
 };
 
 // FINAL (the last block): the head's 1x1 convolution 64 -> 2 (bg_planner.py:43,54; no activation) is
@@ -934,8 +936,360 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_gn_block0_embed: GraphNet's embed convolution (3 -> 64, 3x3, ReLU; bg_planner.py:32,51) fused into the first block.
+//
+// As a launch of its own the embed was 35 us of HBM writes per planner step (151 MB out, read back by block 0).  Here
+// it is ONE K = 32 GEMM per board in front of block 0's 3x3: the producer warps expand the bitboards into an im2col
+// one-hot tile (row = position, k = 3 * tap + plane, 27 of 32 used), two N = 64 UMMAs per M half put the result into
+// tensor memory, eight extra epilogue warps apply bias + ReLU and write bf16 straight into the 3x3's input slab in
+// shared memory -- the slab that k_gn_block_pairs fetches from HBM.  Everything after that is k_gn_block_pairs.
+//
+// Tensor memory has no spare columns (2 buffers x 2 halves x [D_a | D_b]), so the embed result of board m lives in
+// D_b of its OWN buffer (m & 1) during the one window in which those columns are idle: after epilogue 1 of board m - 2
+// has consumed the pair partials and before the 1x1 of board m - 2 overwrites them with its accumulator.  In the
+// issuer's instruction stream of board j:
+//     singles(j) | pair row 0 | embed(j + 1) | pair rows 1, 2a | wait epilogue 0 of j + 1 | 1x1(j - 1) | pair row 2b
+// so the slab of board j + 1 is complete ~700 cycles before board j's last UMMA.  The embeds of boards 0 and 1 run in
+// the prologue (their D_b columns are zeroed again by epilogue 0, which the pair UMMAs rely on).
+//   warps 0, 19   im2col producers (M half 0 / 1); warp 0 also loads the weights
+//   warps 1, 10   tcgen05.mma issuers          warps 2-9   epilogues 1 and 2 (as in k_gn_block_pairs)
+//   warps 11-18   epilogue 0: quadrant = warp & 3, M half = (warp - 11) >> 2
+struct GnEmbedCfg {
+    static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
+    static constexpr int PAIR_BYTES = 8 * 128 * 16, SINGLE_BYTES = 8 * 64 * 16;
+    static constexpr int W3_BYTES = 3 * PAIR_BYTES + 3 * SINGLE_BYTES, W1_BYTES = 8 * 64 * 16;
+    static constexpr int I2C_BYTES = 4 * 256 * 16;     // [4 k-groups][256 rows][8 k] bf16
+    static constexpr int WE_BYTES = 4 * 64 * 16;       // [4 k-groups][64 cout][8 k]
+    static constexpr int THREADS = 640;
+    static constexpr int SMEM = 2 * SLAB_BYTES + W3_BYTES + W1_BYTES + 2 * I2C_BYTES + WE_BYTES + 512;
+};
+
+__global__ void __launch_bounds__(GnEmbedCfg::THREADS, 1)
+k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict__ we, const uint8_t *__restrict__ w3,
+                  const uint8_t *__restrict__ w1, const __grid_constant__ GnBlockConsts kc,
+                  uint8_t *__restrict__ out_planes, int G, int rev) {
+    using C = GnEmbedCfg;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *slab = smem;                               // [2][SLAB_BYTES]
+    uint8_t *sw3 = slab + 2 * C::SLAB_BYTES;
+    uint8_t *sw1 = sw3 + C::W3_BYTES;
+    uint8_t *i2c = sw1 + C::W1_BYTES;                   // [2][I2C_BYTES]
+    uint8_t *swe = i2c + 2 * C::I2C_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(swe + C::WE_BYTES);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *d1_full = bars + 4, *d1_empty = bars + 6;
+    uint64_t *mid_full = bars + 8, *mid_empty = bars + 10, *d2_full = bars + 12, *d2_empty = bars + 14;
+    uint64_t *e_full = bars + 16, *e_empty = bars + 18, *de_full = bars + 20;
+    uint64_t *w_full = bars + 22;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 23);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {   // every tcgen05.commit comes twice: one per issuer warp (M half)
+            ptx::mbar_init(&a_full[i], 8);   ptx::mbar_init(&a_empty[i], 2);     // slab: written by the 8 epilogue-0 warps
+            ptx::mbar_init(&d1_full[i], 2);  ptx::mbar_init(&d1_empty[i], 8);
+            ptx::mbar_init(&mid_full[i], 8); ptx::mbar_init(&mid_empty[i], 2);
+            ptx::mbar_init(&d2_full[i], 2);  ptx::mbar_init(&d2_empty[i], 8);
+            ptx::mbar_init(&e_full[i], 2);   ptx::mbar_init(&e_empty[i], 2);     // im2col tile: two producer warps
+            ptx::mbar_init(&de_full[i], 2);
+        }
+        ptx::mbar_init(w_full, 1);
+        ptx::fence_mbar_init();
+    }
+    // the slab rows outside the board (and everything the epilogue never writes) stay zero for the whole kernel
+    for (int i = threadIdx.x; i < 2 * C::SLAB_BYTES / 16; i += C::THREADS)
+        reinterpret_cast<uint4 *>(slab)[i] = make_uint4(0u, 0u, 0u, 0u);
+    ptx::fence_proxy_async();
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int n_it = blockIdx.x < G ? (G - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+    auto acc_of = [&](int ab, int h) { return tmem_base + (uint32_t)(ab * 256 + h * 128); };   // [D_a | D_b]
+    auto board_of = [&](int it) { const int b = blockIdx.x + it * (int)gridDim.x; return rev ? G - 1 - b : b; };
+
+    if (warp == 0 || warp == 19) {
+        // ================= im2col producers: M half hh = tile rows [128 hh, 128 hh + 128) =================
+        const int hh = warp == 0 ? 0 : 1;
+        if (warp == 0 && lane == 0) {
+            ptx::mbar_expect_tx(w_full, C::W3_BYTES + C::W1_BYTES + C::WE_BYTES);
+            for (int t = 0; t < 9; ++t) ptx::bulk_g2s(sw3 + t * 8192, w3 + t * 8192, 8192, w_full);
+            ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
+            ptx::bulk_g2s(swe, we, C::WE_BYTES, w_full);
+        }
+        // every lane holds the whole position: 8 words per colour (one broadcast load each), fetched one board ahead
+        auto load_words = [&](int it, uint4 *q) {
+            if (it < n_it) {
+                const uint4 *src = reinterpret_cast<const uint4 *>(boards[board_of(it)].stones);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) q[i] = src[i];
+            }
+        };
+        uint4 q[4];
+        load_words(0, q);
+        auto produce = [&](auto HH) {       // the M half as a compile-time constant: X[][] stays in registers
+            constexpr int hh_c = decltype(HH)::value;
+            for (int it = 0; it < n_it; ++it) {
+                const int eb = it & 1;
+                // X[c][1 + j] = word j of plane c (black, white, empty); X[c][0] = X[c][9] = 0: the board's zero surround
+                uint32_t X[3][10];
+                {
+                    const uint32_t bw[8] = {q[0].x, q[0].y, q[0].z, q[0].w, q[1].x, q[1].y, q[1].z, q[1].w};
+                    const uint32_t ww[8] = {q[2].x, q[2].y, q[2].z, q[2].w, q[3].x, q[3].y, q[3].z, q[3].w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        X[0][1 + j] = bw[j];
+                        X[1][1 + j] = ww[j];
+                        X[2][1 + j] = ~(bw[j] | ww[j]) & (j == 7 ? 0x00007FFFu : 0x7FFF7FFFu);
+                    }
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) X[c][0] = X[c][9] = 0u;
+                }
+                load_words(it + 1, q);
+                if (lane == 0) ptx::mbar_wait(&e_empty[eb], ((it >> 1) & 1) ^ 1);
+                __syncwarp();
+                uint8_t *dst = i2c + eb * C::I2C_BYTES;
+#pragma unroll
+                for (int kq = 0; kq < 4; ++kq) {
+                    constexpr int kbase = 4 * hh_c;
+                    const int kk = kbase + kq;              // tile rows 32 kk + lane = board bit index (16 * row + col)
+                    uint32_t v[32];
+#pragma unroll
+                    for (int k = 27; k < 32; ++k) v[k] = 0u;
+#pragma unroll
+                    for (int tap = 0; tap < 9; ++tap) {
+                        const int off = 16 * (tap / 3 - 1) + (tap % 3 - 1);
+                        // 32-bit window of the plane starting at bit 32 kk + off
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            uint32_t win;
+                            if (off < 0) win = __funnelshift_r(X[c][kk], X[c][kk + 1], 32 + off);
+                            else if (off == 0) win = X[c][kk + 1];
+                            else win = __funnelshift_r(X[c][kk + 1], X[c][kk + 2], off);
+                            v[3 * tap + c] = (win >> lane) & 1u;
+                        }
+                    }
+                    const int m = 32 * kk + lane;
+#pragma unroll
+                    for (int cg = 0; cg < 4; ++cg) {
+                        uint32_t pk[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            pk[i] = v[8 * cg + 2 * i] * 0x3F80u + v[8 * cg + 2 * i + 1] * 0x3F800000u;
+                        *reinterpret_cast<uint4 *>(dst + ((size_t)cg * 256 + m) * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    }
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&e_full[eb]);
+            }
+        };
+        if (hh == 0) produce(std::integral_constant<int, 0>()); else produce(std::integral_constant<int, 1>());
+    } else if (warp == 1 || warp == 10) {
+        // ================= tcgen05.mma issuers, one per M half =================
+        const int h = warp == 1 ? 0 : 1;
+        constexpr uint32_t idesc64 = ptx::make_idesc_bf16(128, 64), idesc128 = ptx::make_idesc_bf16(128, 128);
+        constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_S = 64 * 16, LBO_P = 128 * 16, LBO_E = 256 * 16;
+        ptx::mbar_wait(w_full, 0);
+        const uint64_t dpair0 = ptx::make_desc(ptx::smem_u32(sw3), LBO_P, 128);
+        const uint64_t dsing0 = ptx::make_desc(ptx::smem_u32(sw3) + 3 * C::PAIR_BYTES, LBO_S, 128);
+        const uint64_t dw0 = ptx::make_desc(ptx::smem_u32(sw1), LBO_S, 128);
+        const uint64_t dwe0 = ptx::make_desc(ptx::smem_u32(swe), LBO_S, 128);
+        // embed of board m: D_b of buffer m & 1 = im2col tile (K = 32: two K steps) x embed weights
+        auto issue_embed = [&](int m) {
+            const int eb = m & 1;
+            ptx::mbar_wait(&e_full[eb], (m >> 1) & 1);
+            ptx::tc_fence_after();
+            const uint64_t de = ptx::make_desc(ptx::smem_u32(i2c + eb * C::I2C_BYTES), LBO_E, 128) + (uint64_t)(128 * h);
+            const uint32_t acc = acc_of(eb, h) + 64;
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks)
+                ptx::umma_bf16_elect(acc, de + (uint64_t)(2 * ks * 256), dwe0 + (uint64_t)((2 * ks * (int)LBO_S) >> 4), idesc64,
+                                     ks != 0);
+            ptx::umma_commit_elect(&e_empty[eb]);
+            ptx::umma_commit_elect(&de_full[eb]);
+        };
+        auto issue_1x1 = [&](int j) {          // D2 = the D_b columns of board j's own buffer
+            const int jb = j & 1;
+            ptx::mbar_wait(&mid_full[jb], (j >> 1) & 1);
+            ptx::tc_fence_after();
+            const uint32_t acc = acc_of(jb, h);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                ptx::umma_bf16_ts_elect(acc + 64, acc + 8 * k, dw0 + (uint64_t)((2 * k * (int)LBO_S) >> 4), idesc64, k != 0);
+            ptx::umma_commit_elect(&mid_empty[jb]);
+            ptx::umma_commit_elect(&d2_full[jb]);
+        };
+        // prologue: the embeds of boards 0 and 1 (their D_b columns were zeroed by warps 2-9: d2_empty, first phase)
+        for (int m = 0; m < 2 && m < n_it; ++m) {
+            ptx::mbar_wait(&d2_empty[m], 0);
+            ptx::tc_fence_after();
+            issue_embed(m);
+        }
+        if (n_it > 0) { ptx::mbar_wait(&a_full[0], 0); ptx::tc_fence_after(); }     // slab 0 written by epilogue 0
+        for (int it = 0; it < n_it; ++it) {
+            const int ab = it & 1;
+            const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
+            const uint32_t acc = acc_of(ab, h);
+            // singles first: the dx = +1 taps, N = 64 into D_a; the very first one initialises D_a
+#pragma unroll
+            for (int ty = 0; ty < 3; ++ty) {
+                const int rowoff = 17 + 16 * (ty - 1) + 1;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    ptx::umma_bf16_elect(acc, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff),
+                                         dsing0 + (uint64_t)((ty * C::SINGLE_BYTES + 2 * k * (int)LBO_S) >> 4), idesc64,
+                                         (ty | k) != 0);
+            }
+            // pairs accumulate into [D_a | D_b]; D_b was zeroed by epilogue 2 of board it - 2 (epilogue 0 for it < 2)
+            ptx::mbar_wait(&d2_empty[ab], (it >> 1) & 1);
+            ptx::tc_fence_after();
+#define GZ_GN_PAIR(TY, K0, K1)                                                                                     \
+            _Pragma("unroll") for (int k = K0; k < K1; ++k)                                                        \
+                ptx::umma_bf16_elect(acc, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + 17 + 16 * (TY - 1)),            \
+                                     dpair0 + (uint64_t)((TY * C::PAIR_BYTES + 2 * k * (int)LBO_P) >> 4), idesc128, 1u);
+            GZ_GN_PAIR(0, 0, 4)
+            if (it >= 1 && it + 1 < n_it) {
+                // embed(it + 1) into D_b of the other buffer: free once epilogue 1 of board it - 1 has read the pair
+                // partials (mid_full) and until the 1x1 of board it - 1, issued below, writes its accumulator there
+                ptx::mbar_wait(&mid_full[ab ^ 1], ((it - 1) >> 1) & 1);
+                ptx::tc_fence_after();
+                issue_embed(it + 1);
+            }
+            GZ_GN_PAIR(1, 0, 4)
+            GZ_GN_PAIR(2, 0, 2)
+            if (it + 1 < n_it) {   // epilogue 0 of board it + 1 has read the embed result and written the slab
+                ptx::mbar_wait(&a_full[ab ^ 1], ((it + 1) >> 1) & 1);
+                ptx::tc_fence_after();
+            }
+            if (it > 0) issue_1x1(it - 1);
+            if (it + 1 < n_it) {   // D_a of the other buffer free: epilogue 1 of board it - 1
+                ptx::mbar_wait(&d1_empty[ab ^ 1], (((it + 1) >> 1) & 1) ^ 1);
+                ptx::tc_fence_after();
+            }
+            GZ_GN_PAIR(2, 2, 4)
+#undef GZ_GN_PAIR
+            ptx::umma_commit_elect(&a_empty[ab]);
+            ptx::umma_commit_elect(&d1_full[ab]);
+        }
+        if (n_it > 0) issue_1x1(n_it - 1);
+    } else if (warp >= 11) {
+        // ================= epilogue 0: embed result (TMEM) -> bias, ReLU, bf16 -> the 3x3's input slab =================
+        const int q = warp & 3, h0 = (warp - 11) >> 2;
+        const int row = 128 * h0 + 32 * q + lane;           // tile row = plane position - 16
+        const int pos = 16 + row;
+        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h0 * 128 + 64;
+        const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        for (int m = 0; m < n_it; ++m) {
+            const int eb = m & 1;
+            ptx::mbar_wait(&de_full[eb], (m >> 1) & 1);
+            ptx::mbar_wait(&a_empty[eb], ((m >> 1) & 1) ^ 1);          // the 3x3 of board m - 2 has read this slab
+            ptx::tc_fence_after();
+            const uint32_t td = tlane + eb * 256;
+            uint8_t *dst = slab + eb * C::SLAB_BYTES + (size_t)(pos + 1) * 16;
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float v[16];
+                ptx::tmem_ld16(td + c0, v);
+                uint32_t pk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + kc.be[c0 + 2 * i], 0.f),
+                                                   fmaxf(v[2 * i + 1] + kc.be[c0 + 2 * i + 1], 0.f)) : 0u;
+                *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * C::SLAB_ROWS * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * C::SLAB_ROWS * 16) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+            if (m < 2) {   // no 1x1 / epilogue 2 has passed over these columns yet: hand them to the pair UMMAs as zeros
+#pragma unroll
+                for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td + c, zeros);
+                ptx::tmem_wait_st();
+            }
+            ptx::fence_proxy_async();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&a_full[eb]);
+        }
+    } else {
+        // ================= epilogues 1 and 2 (k_gn_block_pairs) =================
+        const int q = warp & 3, h = (warp - 2) >> 2;
+        const int row = 128 * h + 32 * q + lane;
+        const int pos = 16 + row;
+        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 128;
+        const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int ab = 0; ab < 2; ++ab)
+#pragma unroll
+            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(tlane + ab * 256 + 64 + c, zeros);
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { ptx::mbar_arrive(&d2_empty[0]); ptx::mbar_arrive(&d2_empty[1]); }
+        for (int it = 0; it <= n_it; ++it) {
+            if (it > 0) {   // epilogue 2 of board it - 1
+                const int j = it - 1, jb = j & 1;
+                const int b = board_of(j);
+                ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
+                ptx::tc_fence_after();
+                const uint32_t td2 = tlane + jb * 256 + 64;
+                uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float v[16];
+                    ptx::tmem_ld16(td2 + c0, v);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + kc.b1[c0 + 2 * i], 0.f),
+                                                       fmaxf(v[2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
+                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+#pragma unroll
+                for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td2 + c, zeros);
+                ptx::tmem_wait_st();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+            }
+            if (it < n_it) {   // epilogue 1 of board it: out[m] = D_a[m] + D_b[m - 1], bias, ReLU, bf16, in place
+                const int ab = it & 1;
+                const uint32_t par = (it >> 1) & 1;
+                ptx::mbar_wait(&d1_full[ab], par);
+                ptx::mbar_wait(&mid_empty[ab], par ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t td1 = tlane + ab * 256;
+#pragma unroll
+                for (int c0 = 0; c0 < 64; c0 += 16) {
+                    float va[16], vb[16];
+                    tmem_ld16x2(td1 + c0, td1 + 64 + c0, va, vb);
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        float up = __shfl_up_sync(0xffffffffu, vb[i], 1);
+                        if (lane == 0) up = 0.f;
+                        va[i] = fmaxf(va[i] + up + kc.b3[c0 + i], 0.f);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = ptx::pack_bf16(va[2 * i], va[2 * i + 1]);
+                    ptx::tmem_st8(td1 + c0 / 2, pk);
+                }
+                ptx::tmem_wait_st();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
 static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *out, uint8_t *head_out, int G,
-                            cudaStream_t s) {
+                            cudaStream_t s, int direction) {
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(k_gn_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnBlockCfg::SMEM);
@@ -946,7 +1300,7 @@ static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *ou
         cudaFuncSetAttribute(k_gn_block_pairs<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, GnPairsCfg<3>::SMEM);
         configured = true;
     }
-    GnBlockConsts kc;
+    GnBlockConsts kc = {};
     memcpy(kc.b3, e.bw.gn_host_bias[block], sizeof(float) * 128);   // b3 then b1
     memcpy(kc.head_w, e.bw.gn_host_head, sizeof(float) * 130);       // head_w then head_b
     const uint8_t *w1 = e.bw.gn_l1_w[block];
@@ -954,7 +1308,7 @@ static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *ou
     static const bool pairs = !(getenv("GZ_GN_PAIRS") && atoi(getenv("GZ_GN_PAIRS")) == 0);   // A/B switch for profiling
     static const int nslab = getenv("GZ_GN_SLABS") ? atoi(getenv("GZ_GN_SLABS")) : 3;                // A/B switches
     static const bool alternate = !(getenv("GZ_GN_ALTERNATE") && atoi(getenv("GZ_GN_ALTERNATE")) == 0);
-    const int rev = alternate ? (block & 1) ^ 1 : 0;   // the embed writes ascending: block 0 walks back, block 1 forth, ...
+    const int rev = alternate ? direction : 0;   // the layer before walked the other way
     if (pairs) {
         const uint8_t *w3 = e.bw.gn_l3p_w[block];
         if (nslab == 3) {
@@ -1014,11 +1368,32 @@ void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active
 void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s) {
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1];
+    static const bool fused = !(getenv("GZ_GN_FUSED_EMBED") && atoi(getenv("GZ_GN_FUSED_EMBED")) == 0);   // A/B switch
+    if (fused) {
+        // embed + block 0 in one launch (k_gn_block0_embed), then blocks 1-3: p1 -> p0 -> p1 -> head operand
+        static bool configured = false;
+        if (!configured) {
+            cudaFuncSetAttribute(k_gn_block0_embed, cudaFuncAttributeMaxDynamicSharedMemorySize, GnEmbedCfg::SMEM);
+            configured = true;
+        }
+        prof_begin(e, GZ_STAGE_GN_CONVS, 4, s);
+        GnBlockConsts kc;
+        memcpy(kc.b3, w.gn_host_bias[0], sizeof(float) * 128);
+        memcpy(kc.head_w, w.gn_host_head, sizeof(float) * 130);
+        memcpy(kc.be, w.gn_host_embed_bias, sizeof(float) * 64);
+        const int grid = G < e.sm_count ? G : e.sm_count;
+        k_gn_block0_embed<<<grid, GnEmbedCfg::THREADS, GnEmbedCfg::SMEM, s>>>(boards, w.gn_embed_i2c_w, w.gn_l3p_w[0],
+                                                                              w.gn_l1_w[0], kc, p1, G, 0);
+        for (int i = 1; i < 4; ++i)
+            launch_gn_block(e, (i & 1) ? p1 : p0, i, (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s, i & 1);
+        prof_end(e, s);
+        return;
+    }
     prof_begin(e, GZ_STAGE_GN_CONVS, 5, s);
     launch_conv<16, 64, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.gn_embed_w,
                                               e.gn.embed.b, nullptr, p0, active, G, s);
     for (int i = 0; i < 4; ++i) {   // p0 -> p1 -> p0 -> p1 -> p0
-        launch_gn_block(e, (i & 1) ? p1 : p0, i, (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s);
+        launch_gn_block(e, (i & 1) ? p1 : p0, i, (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s, (i & 1) ^ 1);
     }
     prof_end(e, s);
 }

@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+python -m pytest tests/test_gpu_bf16.py tests/test_gpu_timed_path.py tests/test_gpu_edge_cases.py -q -x -k "not outcome_rates and not fp32_bit_exact" > gpurun_out/r02n_pytest.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/r02n_pytest.log; tail -3 gpurun_out/r02n_pytest.log
+for A in 1 0 1; do
+GZ_GN_ALTERNATE=$A python bench.py --steps 4 --warmup 3 --selfplay-plies 0 --s400-steps 0 --cpu-seconds 1 --port-only > gpurun_out/r02n_a$A.json 2> gpurun_out/r02n_a$A.err
+python -c "
+import json; d=json.loads(open('gpurun_out/r02n_a$A.json').read().strip().splitlines()[-1]); print('alt $A', round(d['value']), round(d['ms_per_step'],1), d['roofline']['frac'], d['roofline']['stage_ms'], d['clocks']['sm_mhz'])"
+done
