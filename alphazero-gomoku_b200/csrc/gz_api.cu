@@ -239,14 +239,17 @@ static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const fl
                     f2bf((float)((double)w[((size_t)co * 3 + ci) * 9 + tap] * scale));
         }
 }
-// GraphNet embed [64][3][3][3] as one im2col GEMM operand for k_gn_block0_embed: K = 27 (k = 3 * tap + plane, plane =
-// black / white / empty) padded to 32 -> [4 k-groups][64 cout][8 k] bf16
+// GraphNet embed [64][3][3][3] as one im2col GEMM operand for k_gn_block0_embed: K = 27 padded to 32, in the order the
+// kernel's producer builds the one-hot tile in: k = 3 * (3 * plane + ky) + kx (plane = black / white / empty)
+// -> [4 k-groups][64 cout][8 k] bf16
 static void pack_embed_im2col_bf16(std::vector<uint16_t> &out, const float *w) {
     size_t base = out.size();
     out.resize(base + (size_t)4 * 64 * 8, 0);
-    for (int k = 0; k < 27; ++k)
+    for (int k = 0; k < 27; ++k) {
+        const int plane = k / 9, ky = (k / 3) % 3, kx = k % 3;
         for (int co = 0; co < 64; ++co)
-            out[base + ((size_t)(k >> 3) * 64 + co) * 8 + (k & 7)] = f2bf(w[((size_t)co * 3 + k % 3) * 9 + k / 3]);
+            out[base + ((size_t)(k >> 3) * 64 + co) * 8 + (k & 7)] = f2bf(w[((size_t)co * 3 + plane) * 9 + ky * 3 + kx]);
+    }
 }
 // linear weight [nout][nin] -> K-chunks of 64 inputs: [chunk][8 k-groups][256 n][8 k] bf16, zero padded
 static void pack_fc_bf16(std::vector<uint16_t> &out, const float *w, int nout, int nin, int chunks, int npad = 256) {

@@ -953,8 +953,12 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
 // so the slab of board j + 1 is complete ~700 cycles before board j's last UMMA.  The embeds of boards 0 and 1 run in
 // the prologue (their D_b columns are zeroed again by epilogue 0, which the pair UMMAs rely on).
 //   warps 0, 19   im2col producers (M half 0 / 1); warp 0 also loads the weights
-//   warps 1, 10   tcgen05.mma issuers          warps 2-9   epilogues 1 and 2 (as in k_gn_block_pairs)
-//   warps 11-18   epilogue 0: quadrant = warp & 3, M half = (warp - 11) >> 2
+//   warps 1, 10   tcgen05.mma issuers          warps 2-9   epilogue 1 (3x3 accumulators -> bf16 A operand of the 1x1)
+//   warps 11-18   epilogue 0 (embed -> slab) and epilogue 2 (1x1 -> planes): quadrant = warp & 3, M half = (warp - 11) >> 2
+// Measured (profiles/r02_gn_block0_embed.md): 84 us against 35 + 66 us for the two launches it replaces.  Per board the
+// epilogues now read 256 KB from tensor memory (64 embed + 128 pair partials + 64 1x1) against 192 KB in
+// k_gn_block_pairs, and both kernels run at ~56 B of tcgen05.ld per clock: tensor-memory READ bandwidth, not the
+// tensor pipe, is what paces them.
 struct GnEmbedCfg {
     static constexpr int SLAB_ROWS = 290, SLAB_BYTES = 8 * SLAB_ROWS * 16;
     static constexpr int PAIR_BYTES = 8 * 128 * 16, SINGLE_BYTES = 8 * 64 * 16;
@@ -1030,10 +1034,11 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
         load_words(0, q);
         auto produce = [&](auto HH) {       // the M half as a compile-time constant: X[][] stays in registers
             constexpr int hh_c = decltype(HH)::value;
+            GN_T(long long p_wait = 0, p_work = 0;)
             for (int it = 0; it < n_it; ++it) {
                 const int eb = it & 1;
-                // X[c][1 + j] = word j of plane c (black, white, empty); X[c][0] = X[c][9] = 0: the board's zero surround
-                uint32_t X[3][10];
+                // X[c][1 + j] = word j of plane c (black, white, empty); X[c][0], X[c][9], X[c][10] = 0: the zero surround
+                uint32_t X[3][11];
                 {
                     const uint32_t bw[8] = {q[0].x, q[0].y, q[0].z, q[0].w, q[1].x, q[1].y, q[1].z, q[1].w};
                     const uint32_t ww[8] = {q[2].x, q[2].y, q[2].z, q[2].w, q[3].x, q[3].y, q[3].z, q[3].w};
@@ -1044,46 +1049,55 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
                         X[2][1 + j] = ~(bw[j] | ww[j]) & (j == 7 ? 0x00007FFFu : 0x7FFF7FFFu);
                     }
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) X[c][0] = X[c][9] = 0u;
+                    for (int c = 0; c < 3; ++c) X[c][0] = X[c][9] = X[c][10] = 0u;
                 }
                 load_words(it + 1, q);
+                GN_T(const long long tp0 = clock64();)
                 if (lane == 0) ptx::mbar_wait(&e_empty[eb], ((it >> 1) & 1) ^ 1);
                 __syncwarp();
+                GN_T(const long long tp1 = clock64(); p_wait += tp1 - tp0;)
                 uint8_t *dst = i2c + eb * C::I2C_BYTES;
 #pragma unroll
                 for (int kq = 0; kq < 4; ++kq) {
                     constexpr int kbase = 4 * hh_c;
                     const int kk = kbase + kq;              // tile rows 32 kk + lane = board bit index (16 * row + col)
-                    uint32_t v[32];
+                    // t[3 c + ky]: the three cells (dx = -1, 0, +1) of plane c in board row + ky - 1 around this lane's
+                    // cell = bits lane .. lane + 2 of the plane's 64-bit window that starts at bit 32 kk + 16 (ky - 1) - 1
+                    uint32_t t[9];
 #pragma unroll
-                    for (int k = 27; k < 32; ++k) v[k] = 0u;
+                    for (int c = 0; c < 3; ++c)
 #pragma unroll
-                    for (int tap = 0; tap < 9; ++tap) {
-                        const int off = 16 * (tap / 3 - 1) + (tap % 3 - 1);
-                        // 32-bit window of the plane starting at bit 32 kk + off
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            uint32_t win;
-                            if (off < 0) win = __funnelshift_r(X[c][kk], X[c][kk + 1], 32 + off);
-                            else if (off == 0) win = X[c][kk + 1];
-                            else win = __funnelshift_r(X[c][kk + 1], X[c][kk + 2], off);
-                            v[3 * tap + c] = (win >> lane) & 1u;
+                        for (int ky = 0; ky < 3; ++ky) {
+                            const int s = 32 * kk + 16 * (ky - 1) - 1 + 32;      // + 32: index into X[c][] (one zero word in front)
+                            const int j0 = s >> 5, sh = s & 31;
+                            const uint32_t lo = __funnelshift_r(X[c][j0], X[c][j0 + 1], sh);
+                            const uint32_t hi = __funnelshift_r(X[c][j0 + 1], X[c][j0 + 2], sh);
+                            t[3 * c + ky] = __funnelshift_r(lo, hi, lane);
                         }
-                    }
+                    // K index k = 3 * (3 c + ky) + kx (pack_embed_im2col_bf16 packs the weights in the same order);
+                    // bf16 1.0 = 0x3F80: a set bit j of t becomes (t & (1 << j)) * (0x3F80 >> j)
                     const int m = 32 * kk + lane;
 #pragma unroll
                     for (int cg = 0; cg < 4; ++cg) {
                         uint32_t pk[4];
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            pk[i] = v[8 * cg + 2 * i] * 0x3F80u + v[8 * cg + 2 * i + 1] * 0x3F800000u;
+                        for (int i = 0; i < 4; ++i) {
+                            const int k0 = 8 * cg + 2 * i, k1 = k0 + 1;
+                            uint32_t w = 0u;
+                            if (k0 < 27) w = (t[k0 / 3] & (1u << (k0 % 3))) * (0x3F80u >> (k0 % 3));
+                            if (k1 < 27) w += (t[k1 / 3] & (1u << (k1 % 3))) * (0x3F800000u >> (k1 % 3));
+                            pk[i] = w;
+                        }
                         *reinterpret_cast<uint4 *>(dst + ((size_t)cg * 256 + m) * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     }
                 }
                 ptx::fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&e_full[eb]);
+                GN_T(p_work += clock64() - tp1;)
             }
+            GN_T(if (blockIdx.x == 0 && lane == 0 && n_it > 0)
+                     printf("gn0 producer %d: per board: wait e_empty %lld, build %lld\n", hh_c, p_wait / n_it, p_work / n_it);)
         };
         if (hh == 0) produce(std::integral_constant<int, 0>()); else produce(std::integral_constant<int, 1>());
     } else if (warp == 1 || warp == 10) {
@@ -1091,6 +1105,7 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
         const int h = warp == 1 ? 0 : 1;
         constexpr uint32_t idesc64 = ptx::make_idesc_bf16(128, 64), idesc128 = ptx::make_idesc_bf16(128, 128);
         constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_S = 64 * 16, LBO_P = 128 * 16, LBO_E = 256 * 16;
+        GN_T(const long long tk0 = clock64(); long long w_ef = 0, w_mfe = 0, w_af = 0, w_d2e = 0, w_d1e = 0, w_mf1 = 0, t_loop = 0;)
         ptx::mbar_wait(w_full, 0);
         const uint64_t dpair0 = ptx::make_desc(ptx::smem_u32(sw3), LBO_P, 128);
         const uint64_t dsing0 = ptx::make_desc(ptx::smem_u32(sw3) + 3 * C::PAIR_BYTES, LBO_S, 128);
@@ -1099,7 +1114,9 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
         // embed of board m: D_b of buffer m & 1 = im2col tile (K = 32: two K steps) x embed weights
         auto issue_embed = [&](int m) {
             const int eb = m & 1;
+            GN_T(const long long t0 = clock64();)
             ptx::mbar_wait(&e_full[eb], (m >> 1) & 1);
+            GN_T(w_ef += clock64() - t0;)
             ptx::tc_fence_after();
             const uint64_t de = ptx::make_desc(ptx::smem_u32(i2c + eb * C::I2C_BYTES), LBO_E, 128) + (uint64_t)(128 * h);
             const uint32_t acc = acc_of(eb, h) + 64;
@@ -1112,7 +1129,9 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
         };
         auto issue_1x1 = [&](int j) {          // D2 = the D_b columns of board j's own buffer
             const int jb = j & 1;
+            GN_T(const long long t0 = clock64();)
             ptx::mbar_wait(&mid_full[jb], (j >> 1) & 1);
+            GN_T(w_mf1 += clock64() - t0;)
             ptx::tc_fence_after();
             const uint32_t acc = acc_of(jb, h);
 #pragma unroll
@@ -1130,6 +1149,7 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
         if (n_it > 0) { ptx::mbar_wait(&a_full[0], 0); ptx::tc_fence_after(); }     // slab 0 written by epilogue 0
         for (int it = 0; it < n_it; ++it) {
             const int ab = it & 1;
+            GN_T(const long long tl0 = clock64();)
             const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
             const uint32_t acc = acc_of(ab, h);
             // singles first: the dx = +1 taps, N = 64 into D_a; the very first one initialises D_a
@@ -1143,7 +1163,9 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
                                          (ty | k) != 0);
             }
             // pairs accumulate into [D_a | D_b]; D_b was zeroed by epilogue 2 of board it - 2 (epilogue 0 for it < 2)
+            GN_T(const long long t3 = clock64();)
             ptx::mbar_wait(&d2_empty[ab], (it >> 1) & 1);
+            GN_T(w_d2e += clock64() - t3;)
             ptx::tc_fence_after();
 #define GZ_GN_PAIR(TY, K0, K1)                                                                                     \
             _Pragma("unroll") for (int k = K0; k < K1; ++k)                                                        \
@@ -1153,53 +1175,77 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             if (it >= 1 && it + 1 < n_it) {
                 // embed(it + 1) into D_b of the other buffer: free once epilogue 1 of board it - 1 has read the pair
                 // partials (mid_full) and until the 1x1 of board it - 1, issued below, writes its accumulator there
+                GN_T(const long long t4 = clock64();)
                 ptx::mbar_wait(&mid_full[ab ^ 1], ((it - 1) >> 1) & 1);
+                GN_T(w_mfe += clock64() - t4;)
                 ptx::tc_fence_after();
                 issue_embed(it + 1);
             }
             GZ_GN_PAIR(1, 0, 4)
             GZ_GN_PAIR(2, 0, 2)
             if (it + 1 < n_it) {   // epilogue 0 of board it + 1 has read the embed result and written the slab
+                GN_T(const long long t5 = clock64();)
                 ptx::mbar_wait(&a_full[ab ^ 1], ((it + 1) >> 1) & 1);
+                GN_T(w_af += clock64() - t5;)
                 ptx::tc_fence_after();
             }
             if (it > 0) issue_1x1(it - 1);
             if (it + 1 < n_it) {   // D_a of the other buffer free: epilogue 1 of board it - 1
+                GN_T(const long long t6 = clock64();)
                 ptx::mbar_wait(&d1_empty[ab ^ 1], (((it + 1) >> 1) & 1) ^ 1);
+                GN_T(w_d1e += clock64() - t6;)
                 ptx::tc_fence_after();
             }
             GZ_GN_PAIR(2, 2, 4)
 #undef GZ_GN_PAIR
             ptx::umma_commit_elect(&a_empty[ab]);
             ptx::umma_commit_elect(&d1_full[ab]);
+            GN_T(t_loop += clock64() - tl0;)
         }
         if (n_it > 0) issue_1x1(n_it - 1);
+        GN_T(if (blockIdx.x == 0 && lane == 0 && n_it > 0)
+                 printf("gn0 issuer h=%d: %d boards, total %lld | per board: loop %lld, wait e_full %lld, mid_full(embed) %lld, a_full %lld, d2_empty %lld, d1_empty %lld, mid_full(1x1) %lld\n",
+                        h, n_it, clock64() - tk0, t_loop / n_it, w_ef / n_it, w_mfe / n_it, w_af / n_it, w_d2e / n_it, w_d1e / n_it, w_mf1 / n_it);)
     } else if (warp >= 11) {
-        // ================= epilogue 0: embed result (TMEM) -> bias, ReLU, bf16 -> the 3x3's input slab =================
+        // ================= epilogue 0 (embed -> slab) and epilogue 2 (1x1 -> planes); quadrant = warp & 3 =================
+        // Epilogue 1 has warps of its own (2-9): it gates both the embed's tensor-memory window and the 1x1, and behind
+        // epilogue 2 on the same warps it finished ~1000 cycles later -- a stall of both issuers on every board.
         const int q = warp & 3, h0 = (warp - 11) >> 2;
         const int row = 128 * h0 + 32 * q + lane;           // tile row = plane position - 16
         const int pos = 16 + row;
         const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
-        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h0 * 128 + 64;
+        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h0 * 128 + 64;      // D_b of buffer 0
         const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
-        for (int m = 0; m < n_it; ++m) {
+        GN_T(long long e_w1 = 0, e_w2 = 0, e_work = 0, e2_w = 0, e2_work = 0;)
+        // D_b of both buffers starts at zero (pair UMMAs only accumulate)
+#pragma unroll
+        for (int ab = 0; ab < 2; ++ab)
+#pragma unroll
+            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(tlane + ab * 256 + c, zeros);
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { ptx::mbar_arrive(&d2_empty[0]); ptx::mbar_arrive(&d2_empty[1]); }
+        auto epilogue0 = [&](int m) {
             const int eb = m & 1;
+            GN_T(const long long t0 = clock64();)
             ptx::mbar_wait(&de_full[eb], (m >> 1) & 1);
+            GN_T(const long long t1 = clock64(); e_w1 += t1 - t0;)
             ptx::mbar_wait(&a_empty[eb], ((m >> 1) & 1) ^ 1);          // the 3x3 of board m - 2 has read this slab
+            GN_T(const long long t2 = clock64(); e_w2 += t2 - t1;)
             ptx::tc_fence_after();
             const uint32_t td = tlane + eb * 256;
             uint8_t *dst = slab + eb * C::SLAB_BYTES + (size_t)(pos + 1) * 16;
+            float v[64];
+            ptx::tmem_ld64(td, v);
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {
-                float v[16];
-                ptx::tmem_ld16(td + c0, v);
-                uint32_t pk[8];
+            for (int c0 = 0; c0 < 64; c0 += 8) {
+                uint32_t pk[4];
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + kc.be[c0 + 2 * i], 0.f),
-                                                   fmaxf(v[2 * i + 1] + kc.be[c0 + 2 * i + 1], 0.f)) : 0u;
+                for (int i = 0; i < 4; ++i)
+                    pk[i] = valid ? ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + kc.be[c0 + 2 * i], 0.f),
+                                                   fmaxf(v[c0 + 2 * i + 1] + kc.be[c0 + 2 * i + 1], 0.f)) : 0u;
                 *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * C::SLAB_ROWS * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * C::SLAB_ROWS * 16) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
             }
             if (m < 2) {   // no 1x1 / epilogue 2 has passed over these columns yet: hand them to the pair UMMAs as zeros
 #pragma unroll
@@ -1210,78 +1256,86 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&a_full[eb]);
+            GN_T(e_work += clock64() - t2;)
+        };
+        auto epilogue2 = [&](int j) {
+            const int jb = j & 1;
+            const int b = board_of(j);
+            GN_T(const long long t0 = clock64();)
+            ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
+            GN_T(const long long t1 = clock64(); e2_w += t1 - t0;)
+            ptx::tc_fence_after();
+            const uint32_t td2 = tlane + jb * 256;
+            uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
+            float v[64];
+            ptx::tmem_ld64(td2, v);
+#pragma unroll
+            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td2 + c, zeros);     // hand the columns back as a zeroed D_b
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 8) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    pk[i] = valid ? ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + kc.b1[c0 + 2 * i], 0.f),
+                                                   fmaxf(v[c0 + 2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
+                *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+            ptx::tmem_wait_st();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+            GN_T(e2_work += clock64() - t1;)
+        };
+        // in time: epilogue 0 of boards 0 and 1 (prologue), then during board it's UMMAs epilogue 0 of board it + 1
+        // (the issuers wait for it before the 1x1 of board it - 1) and epilogue 2 of board it - 1
+        if (n_it > 0) epilogue0(0);
+        if (n_it > 1) epilogue0(1);
+        for (int it = 1; it <= n_it; ++it) {
+            if (it + 1 < n_it) epilogue0(it + 1);
+            epilogue2(it - 1);
         }
+        GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 11 || warp == 18) && n_it > 0)
+                 printf("gn0 epilogue-0/2 warp %d: per board: wait de_full %lld, a_empty %lld, epi0 %lld, wait d2_full %lld, epi2 %lld\n",
+                        warp, e_w1 / n_it, e_w2 / n_it, e_work / n_it, e2_w / n_it, e2_work / n_it);)
     } else {
-        // ================= epilogues 1 and 2 (k_gn_block_pairs) =================
+        // ================= epilogue 1 (warps 2-9): out[m] = D_a[m] + D_b[m - 1], bias, ReLU, bf16, in place =================
         const int q = warp & 3, h = (warp - 2) >> 2;
-        const int row = 128 * h + 32 * q + lane;
-        const int pos = 16 + row;
-        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
         const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 128;
-        const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        GN_T(long long w_d1f = 0, w_me = 0, t_e1 = 0;)
+        for (int it = 0; it < n_it; ++it) {
+            const int ab = it & 1;
+            const uint32_t par = (it >> 1) & 1;
+            GN_T(const long long t0 = clock64();)
+            ptx::mbar_wait(&d1_full[ab], par);
+            GN_T(const long long t1 = clock64(); w_d1f += t1 - t0;)
+            ptx::mbar_wait(&mid_empty[ab], par ^ 1);
+            GN_T(const long long t2 = clock64(); w_me += t2 - t1;)
+            ptx::tc_fence_after();
+            const uint32_t td1 = tlane + ab * 256;
 #pragma unroll
-        for (int ab = 0; ab < 2; ++ab)
+            for (int c0 = 0; c0 < 64; c0 += 16) {
+                float va[16], vb[16];
+                tmem_ld16x2(td1 + c0, td1 + 64 + c0, va, vb);
+                uint32_t pk[8];
 #pragma unroll
-            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(tlane + ab * 256 + 64 + c, zeros);
-        ptx::tmem_wait_st();
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) { ptx::mbar_arrive(&d2_empty[0]); ptx::mbar_arrive(&d2_empty[1]); }
-        for (int it = 0; it <= n_it; ++it) {
-            if (it > 0) {   // epilogue 2 of board it - 1
-                const int j = it - 1, jb = j & 1;
-                const int b = board_of(j);
-                ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
-                ptx::tc_fence_after();
-                const uint32_t td2 = tlane + jb * 256 + 64;
-                uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
-#pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
-                    float v[16];
-                    ptx::tmem_ld16(td2 + c0, v);
-                    uint32_t pk[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        pk[i] = valid ? ptx::pack_bf16(fmaxf(v[2 * i] + kc.b1[c0 + 2 * i], 0.f),
-                                                       fmaxf(v[2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
-                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8 + 1) * kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                for (int i = 0; i < 16; ++i) {
+                    float up = __shfl_up_sync(0xffffffffu, vb[i], 1);
+                    if (lane == 0) up = 0.f;     // board column 0: the row above in the tile is the zero padding column
+                    va[i] = fmaxf(va[i] + up + kc.b3[c0 + i], 0.f);
                 }
 #pragma unroll
-                for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td2 + c, zeros);
-                ptx::tmem_wait_st();
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+                for (int i = 0; i < 8; ++i) pk[i] = ptx::pack_bf16(va[2 * i], va[2 * i + 1]);
+                ptx::tmem_st8(td1 + c0 / 2, pk);
             }
-            if (it < n_it) {   // epilogue 1 of board it: out[m] = D_a[m] + D_b[m - 1], bias, ReLU, bf16, in place
-                const int ab = it & 1;
-                const uint32_t par = (it >> 1) & 1;
-                ptx::mbar_wait(&d1_full[ab], par);
-                ptx::mbar_wait(&mid_empty[ab], par ^ 1);
-                ptx::tc_fence_after();
-                const uint32_t td1 = tlane + ab * 256;
-#pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 16) {
-                    float va[16], vb[16];
-                    tmem_ld16x2(td1 + c0, td1 + 64 + c0, va, vb);
-                    uint32_t pk[8];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float up = __shfl_up_sync(0xffffffffu, vb[i], 1);
-                        if (lane == 0) up = 0.f;
-                        va[i] = fmaxf(va[i] + up + kc.b3[c0 + i], 0.f);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) pk[i] = ptx::pack_bf16(va[2 * i], va[2 * i + 1]);
-                    ptx::tmem_st8(td1 + c0 / 2, pk);
-                }
-                ptx::tmem_wait_st();
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
-            }
+            ptx::tmem_wait_st();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
+            GN_T(t_e1 += clock64() - t2;)
         }
+        GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 2 || warp == 9) && n_it > 0)
+                 printf("gn0 epilogue-1 warp %d: per board: wait d1_full %lld, mid_empty %lld, epi1 %lld\n",
+                        warp, w_d1f / n_it, w_me / n_it, t_e1 / n_it);)
     }
     ptx::tc_fence_before();
     __syncthreads();
