@@ -908,11 +908,20 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
 #pragma unroll
                 for (int c0 = 0; c0 < 64; c0 += 16) {
                     float va[16], vb[16];
+#if defined(GZ_EXP_EPI1) && GZ_EXP_EPI1 == 2      // perf experiment (wrong results): no D_b read at all
+                    ptx::tmem_ld16(td1 + c0, va);
+                    for (int i = 0; i < 16; ++i) vb[i] = 0.f;
+#else
                     tmem_ld16x2(td1 + c0, td1 + 64 + c0, va, vb);
+#endif
                     uint32_t pk[8];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
+#if defined(GZ_EXP_EPI1)                          // perf experiment (wrong results): no shuffles
+                        float up = vb[i];
+#else
                         float up = __shfl_up_sync(0xffffffffu, vb[i], 1);
+#endif
                         if (lane == 0) up = 0.f;     // board column 0: the row above in the tile is the zero padding column
                         va[i] = fmaxf(va[i] + up + kc.b3[c0 + i], 0.f);
                     }
