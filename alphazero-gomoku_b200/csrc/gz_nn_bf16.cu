@@ -697,6 +697,32 @@ __device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, float *va,
 // NSLAB input slab buffers (the loads come from HBM: with two, the issuers waited 200-460 cycles per board for a_full).
 // rev: boards are walked from the last to the first.  Consecutive layers alternate the direction, so a layer starts on
 // the boards its predecessor wrote last -- the part of the 151 MB plane buffer that is still in the 126 MB L2.
+// four x16 loads in flight (32 columns of each of two accumulators), one round trip
+__device__ __forceinline__ void tmem_ld32x2(uint32_t ta, uint32_t tb, float *va, float *vb) {
+    uint32_t r[4][16];
+    const uint32_t addr[4] = {ta, ta + 16, tb, tb + 16};
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=r"(r[g][0]), "=r"(r[g][1]), "=r"(r[g][2]), "=r"(r[g][3]), "=r"(r[g][4]), "=r"(r[g][5]), "=r"(r[g][6]),
+              "=r"(r[g][7]), "=r"(r[g][8]), "=r"(r[g][9]), "=r"(r[g][10]), "=r"(r[g][11]), "=r"(r[g][12]), "=r"(r[g][13]),
+              "=r"(r[g][14]), "=r"(r[g][15])
+            : "r"(addr[g]) : "memory");
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(r[g][0]), "+r"(r[g][1]), "+r"(r[g][2]), "+r"(r[g][3]), "+r"(r[g][4]), "+r"(r[g][5]), "+r"(r[g][6]),
+                       "+r"(r[g][7]), "+r"(r[g][8]), "+r"(r[g][9]), "+r"(r[g][10]), "+r"(r[g][11]), "+r"(r[g][12]),
+                       "+r"(r[g][13]), "+r"(r[g][14]), "+r"(r[g][15])
+                     : : "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        va[i] = __uint_as_float(r[0][i]); va[16 + i] = __uint_as_float(r[1][i]);
+        vb[i] = __uint_as_float(r[2][i]); vb[16 + i] = __uint_as_float(r[3][i]);
+    }
+}
+
 template <bool FINAL, int NSLAB>
 __global__ void __launch_bounds__(352, 1)
 k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w3, const uint8_t *__restrict__ w1,
@@ -958,12 +984,13 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
 // D_b of its OWN buffer (m & 1) during the one window in which those columns are idle: after epilogue 1 of board m - 2
 // has consumed the pair partials and before the 1x1 of board m - 2 overwrites them with its accumulator.  In the
 // issuer's instruction stream of board j:
-//     singles(j) | pair row 0 | embed(j + 1) | pair rows 1, 2a | wait epilogue 0 of j + 1 | 1x1(j - 1) | pair row 2b
-// so the slab of board j + 1 is complete ~700 cycles before board j's last UMMA.  The embeds of boards 0 and 1 run in
-// the prologue (their D_b columns are zeroed again by epilogue 0, which the pair UMMAs rely on).
+//     wait epilogue 0 of j | 1x1(j - 2) | singles(j) | embed(j + 1) | pair rows 0, 1, 2
+// The embeds of boards 0 and 1 run in the prologue (their D_b columns are zeroed again by epilogue 0, which the pair
+// UMMAs rely on).
 //   warps 0, 19   im2col producers (M half 0 / 1); warp 0 also loads the weights
-//   warps 1, 10   tcgen05.mma issuers          warps 2-9   epilogue 1 (3x3 accumulators -> bf16 A operand of the 1x1)
-//   warps 11-18   epilogue 0 (embed -> slab) and epilogue 2 (1x1 -> planes): quadrant = warp & 3, M half = (warp - 11) >> 2
+//   warps 1, 10   tcgen05.mma issuers
+//   warps 2-9     epilogue 1 (3x3 accumulators -> bf16 A operand of the 1x1) and epilogue 0 (embed -> slab)
+//   warps 11-18   epilogue 2 (1x1 -> planes): quadrant = warp & 3, M half = (warp - 11) >> 2
 // Measured (profiles/r02_gn_block0_embed.md): 84 us against 35 + 66 us for the two launches it replaces.  Per board the
 // epilogues now read 256 KB from tensor memory (64 embed + 128 pair partials + 64 1x1) against 192 KB in
 // k_gn_block_pairs, and both kernels run at ~56 B of tcgen05.ld per clock: tensor-memory READ bandwidth, not the
@@ -1149,16 +1176,28 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::umma_commit_elect(&mid_empty[jb]);
             ptx::umma_commit_elect(&d2_full[jb]);
         };
-        // prologue: the embeds of boards 0 and 1 (their D_b columns were zeroed by warps 2-9: d2_empty, first phase)
+        // prologue: the embeds of boards 0 and 1 (their D_b columns were zeroed by the epilogue-2 warps: d2_empty, first phase)
         for (int m = 0; m < 2 && m < n_it; ++m) {
             ptx::mbar_wait(&d2_empty[m], 0);
             ptx::tc_fence_after();
             issue_embed(m);
         }
-        if (n_it > 0) { ptx::mbar_wait(&a_full[0], 0); ptx::tc_fence_after(); }     // slab 0 written by epilogue 0
         for (int it = 0; it < n_it; ++it) {
             const int ab = it & 1;
             GN_T(const long long tl0 = clock64();)
+            // slab of board it written by epilogue 0, which has thereby also left the D_b columns of this buffer: the
+            // 1x1 of board it - 2 may put its accumulator there.  It goes first so that everything behind it (epilogue 2,
+            // which hands D_b back zeroed for this board's pair UMMAs) starts as early as possible; the singles below
+            // overwrite its A operand (D_a of this buffer) only after it, the tensor pipe executes in order.
+            GN_T(const long long t5 = clock64();)
+            ptx::mbar_wait(&a_full[ab], (it >> 1) & 1);
+            GN_T(w_af += clock64() - t5;)
+            ptx::tc_fence_after();
+            if (it >= 2) issue_1x1(it - 2);
+            GN_T(const long long t6 = clock64();)
+            ptx::mbar_wait(&d1_empty[ab], ((it >> 1) & 1) ^ 1);      // D_a free: epilogue 1 of board it - 2
+            GN_T(w_d1e += clock64() - t6;)
+            ptx::tc_fence_after();
             const uint64_t da_h = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128) + (uint64_t)(128 * h);
             const uint32_t acc = acc_of(ab, h);
             // singles first: the dx = +1 taps, N = 64 into D_a; the very first one initialises D_a
@@ -1171,6 +1210,15 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
                                          dsing0 + (uint64_t)((ty * C::SINGLE_BYTES + 2 * k * (int)LBO_S) >> 4), idesc64,
                                          (ty | k) != 0);
             }
+            if (it >= 1 && it + 1 < n_it) {
+                // embed(it + 1) into D_b of the other buffer: free once epilogue 1 of board it - 1 has read the pair
+                // partials (mid_full) and until the 1x1 of board it - 1 (top of the next iteration) writes there
+                GN_T(const long long t4 = clock64();)
+                ptx::mbar_wait(&mid_full[ab ^ 1], ((it - 1) >> 1) & 1);
+                GN_T(w_mfe += clock64() - t4;)
+                ptx::tc_fence_after();
+                issue_embed(it + 1);
+            }
             // pairs accumulate into [D_a | D_b]; D_b was zeroed by epilogue 2 of board it - 2 (epilogue 0 for it < 2)
             GN_T(const long long t3 = clock64();)
             ptx::mbar_wait(&d2_empty[ab], (it >> 1) & 1);
@@ -1181,51 +1229,29 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
                 ptx::umma_bf16_elect(acc, da_h + (uint64_t)(2 * k * C::SLAB_ROWS + 17 + 16 * (TY - 1)),            \
                                      dpair0 + (uint64_t)((TY * C::PAIR_BYTES + 2 * k * (int)LBO_P) >> 4), idesc128, 1u);
             GZ_GN_PAIR(0, 0, 4)
-            if (it >= 1 && it + 1 < n_it) {
-                // embed(it + 1) into D_b of the other buffer: free once epilogue 1 of board it - 1 has read the pair
-                // partials (mid_full) and until the 1x1 of board it - 1, issued below, writes its accumulator there
-                GN_T(const long long t4 = clock64();)
-                ptx::mbar_wait(&mid_full[ab ^ 1], ((it - 1) >> 1) & 1);
-                GN_T(w_mfe += clock64() - t4;)
-                ptx::tc_fence_after();
-                issue_embed(it + 1);
-            }
             GZ_GN_PAIR(1, 0, 4)
-            GZ_GN_PAIR(2, 0, 2)
-            if (it + 1 < n_it) {   // epilogue 0 of board it + 1 has read the embed result and written the slab
-                GN_T(const long long t5 = clock64();)
-                ptx::mbar_wait(&a_full[ab ^ 1], ((it + 1) >> 1) & 1);
-                GN_T(w_af += clock64() - t5;)
-                ptx::tc_fence_after();
-            }
-            if (it > 0) issue_1x1(it - 1);
-            if (it + 1 < n_it) {   // D_a of the other buffer free: epilogue 1 of board it - 1
-                GN_T(const long long t6 = clock64();)
-                ptx::mbar_wait(&d1_empty[ab ^ 1], (((it + 1) >> 1) & 1) ^ 1);
-                GN_T(w_d1e += clock64() - t6;)
-                ptx::tc_fence_after();
-            }
-            GZ_GN_PAIR(2, 2, 4)
+            GZ_GN_PAIR(2, 0, 4)
 #undef GZ_GN_PAIR
             ptx::umma_commit_elect(&a_empty[ab]);
             ptx::umma_commit_elect(&d1_full[ab]);
             GN_T(t_loop += clock64() - tl0;)
         }
-        if (n_it > 0) issue_1x1(n_it - 1);
+        if (n_it >= 2) issue_1x1(n_it - 2);
+        if (n_it >= 1) issue_1x1(n_it - 1);
         GN_T(if (blockIdx.x == 0 && lane == 0 && n_it > 0)
                  printf("gn0 issuer h=%d: %d boards, total %lld | per board: loop %lld, wait e_full %lld, mid_full(embed) %lld, a_full %lld, d2_empty %lld, d1_empty %lld, mid_full(1x1) %lld\n",
                         h, n_it, clock64() - tk0, t_loop / n_it, w_ef / n_it, w_mfe / n_it, w_af / n_it, w_d2e / n_it, w_d1e / n_it, w_mf1 / n_it);)
     } else if (warp >= 11) {
-        // ================= epilogue 0 (embed -> slab) and epilogue 2 (1x1 -> planes); quadrant = warp & 3 =================
-        // Epilogue 1 has warps of its own (2-9): it gates both the embed's tensor-memory window and the 1x1, and behind
-        // epilogue 2 on the same warps it finished ~1000 cycles later -- a stall of both issuers on every board.
+        // ================= epilogue 2 (1x1 -> planes); quadrant = warp & 3 =================
+        // Warps of its own: behind epilogue 2 on the same warps, epilogue 1 -- which gates both the embed's tensor-memory
+        // window and the 1x1 -- finished ~1000 cycles later, a stall of both issuers on every board.
         const int q = warp & 3, h0 = (warp - 11) >> 2;
         const int row = 128 * h0 + 32 * q + lane;           // tile row = plane position - 16
         const int pos = 16 + row;
         const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
         const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h0 * 128 + 64;      // D_b of buffer 0
         const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
-        GN_T(long long e_w1 = 0, e_w2 = 0, e_work = 0, e2_w = 0, e2_work = 0;)
+        GN_T(long long e2_w = 0, e2_work = 0;)
         // D_b of both buffers starts at zero (pair UMMAs only accumulate)
 #pragma unroll
         for (int ab = 0; ab < 2; ++ab)
@@ -1235,6 +1261,48 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) { ptx::mbar_arrive(&d2_empty[0]); ptx::mbar_arrive(&d2_empty[1]); }
+        auto epilogue2 = [&](int j) {
+            const int jb = j & 1;
+            const int b = board_of(j);
+            GN_T(const long long t0 = clock64();)
+            ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
+            GN_T(const long long t1 = clock64(); e2_w += t1 - t0;)
+            ptx::tc_fence_after();
+            const uint32_t td2 = tlane + jb * 256;
+            uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
+            float v[64];
+            ptx::tmem_ld64(td2, v);
+            // hand the columns back as a zeroed D_b before anything else: the pair UMMAs of board j + 2 wait for them
+#pragma unroll
+            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td2 + c, zeros);
+            ptx::tmem_wait_st();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 8) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    pk[i] = valid ? ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + kc.b1[c0 + 2 * i], 0.f),
+                                                   fmaxf(v[c0 + 2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
+                *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+            GN_T(e2_work += clock64() - t1;)
+        };
+        for (int j = 0; j < n_it; ++j) epilogue2(j);
+        GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 11 || warp == 18) && n_it > 0)
+                 printf("gn0 epilogue-2 warp %d: per board: wait d2_full %lld, epi2 %lld\n", warp, e2_w / n_it, e2_work / n_it);)
+    } else {
+        // ================= warps 2-9: epilogue 1 (out[m] = D_a[m] + D_b[m - 1], bias, ReLU, bf16, in place) and epilogue 0
+        // (embed -> slab).  The two alternate in time -- epilogue 1 of board it, then epilogue 0 of board it + 2, whose
+        // embed the issuers launch the moment epilogue 1 signals -- so they never compete for tensor-memory reads.
+        const int q = warp & 3, h = (warp - 2) >> 2;
+        const int pos = 16 + 128 * h + 32 * q + lane;
+        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
+        const uint32_t zeros[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 128;
+        GN_T(long long w_d1f = 0, w_me = 0, t_e1 = 0, e_w1 = 0, e_w2 = 0, e_work = 0;)
         auto epilogue0 = [&](int m) {
             const int eb = m & 1;
             GN_T(const long long t0 = clock64();)
@@ -1243,7 +1311,7 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::mbar_wait(&a_empty[eb], ((m >> 1) & 1) ^ 1);          // the 3x3 of board m - 2 has read this slab
             GN_T(const long long t2 = clock64(); e_w2 += t2 - t1;)
             ptx::tc_fence_after();
-            const uint32_t td = tlane + eb * 256;
+            const uint32_t td = tlane + eb * 256 + 64;             // D_b
             uint8_t *dst = slab + eb * C::SLAB_BYTES + (size_t)(pos + 1) * 16;
             float v[64];
             ptx::tmem_ld64(td, v);
@@ -1267,50 +1335,8 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             if (lane == 0) ptx::mbar_arrive(&a_full[eb]);
             GN_T(e_work += clock64() - t2;)
         };
-        auto epilogue2 = [&](int j) {
-            const int jb = j & 1;
-            const int b = board_of(j);
-            GN_T(const long long t0 = clock64();)
-            ptx::mbar_wait(&d2_full[jb], (j >> 1) & 1);
-            GN_T(const long long t1 = clock64(); e2_w += t1 - t0;)
-            ptx::tc_fence_after();
-            const uint32_t td2 = tlane + jb * 256;
-            uint8_t *dst = out_planes + kGuardBytes + (size_t)b * 8 * kPlaneBytes + (size_t)pos * 16;
-            float v[64];
-            ptx::tmem_ld64(td2, v);
-#pragma unroll
-            for (int c = 0; c < 64; c += 8) ptx::tmem_st8(td2 + c, zeros);     // hand the columns back as a zeroed D_b
-#pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 8) {
-                uint32_t pk[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    pk[i] = valid ? ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + kc.b1[c0 + 2 * i], 0.f),
-                                                   fmaxf(v[c0 + 2 * i + 1] + kc.b1[c0 + 2 * i + 1], 0.f)) : 0u;
-                *reinterpret_cast<uint4 *>(dst + (size_t)(c0 / 8) * kPlaneBytes) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            }
-            ptx::tmem_wait_st();
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&d2_empty[jb]);
-            GN_T(e2_work += clock64() - t1;)
-        };
-        // in time: epilogue 0 of boards 0 and 1 (prologue), then during board it's UMMAs epilogue 0 of board it + 1
-        // (the issuers wait for it before the 1x1 of board it - 1) and epilogue 2 of board it - 1
         if (n_it > 0) epilogue0(0);
         if (n_it > 1) epilogue0(1);
-        for (int it = 1; it <= n_it; ++it) {
-            if (it + 1 < n_it) epilogue0(it + 1);
-            epilogue2(it - 1);
-        }
-        GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 11 || warp == 18) && n_it > 0)
-                 printf("gn0 epilogue-0/2 warp %d: per board: wait de_full %lld, a_empty %lld, epi0 %lld, wait d2_full %lld, epi2 %lld\n",
-                        warp, e_w1 / n_it, e_w2 / n_it, e_work / n_it, e2_w / n_it, e2_work / n_it);)
-    } else {
-        // ================= epilogue 1 (warps 2-9): out[m] = D_a[m] + D_b[m - 1], bias, ReLU, bf16, in place =================
-        const int q = warp & 3, h = (warp - 2) >> 2;
-        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h * 128;
-        GN_T(long long w_d1f = 0, w_me = 0, t_e1 = 0;)
         for (int it = 0; it < n_it; ++it) {
             const int ab = it & 1;
             const uint32_t par = (it >> 1) & 1;
@@ -1321,30 +1347,36 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             GN_T(const long long t2 = clock64(); w_me += t2 - t1;)
             ptx::tc_fence_after();
             const uint32_t td1 = tlane + ab * 256;
+            // two round trips of 32 + 32 columns (four were 1950 cycles per board, and this epilogue is on the critical chain
+            // epilogue 1 -> embed -> epilogue 0 -> next board's slab)
 #pragma unroll
-            for (int c0 = 0; c0 < 64; c0 += 16) {
-                float va[16], vb[16];
-                tmem_ld16x2(td1 + c0, td1 + 64 + c0, va, vb);
-                uint32_t pk[8];
+            for (int c0 = 0; c0 < 64; c0 += 32) {
+                float va[32], vb[32];
+                tmem_ld32x2(td1 + c0, td1 + 64 + c0, va, vb);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
+                for (int i = 0; i < 32; ++i) {
                     float up = __shfl_up_sync(0xffffffffu, vb[i], 1);
                     if (lane == 0) up = 0.f;     // board column 0: the row above in the tile is the zero padding column
                     va[i] = fmaxf(va[i] + up + kc.b3[c0 + i], 0.f);
                 }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) pk[i] = ptx::pack_bf16(va[2 * i], va[2 * i + 1]);
-                ptx::tmem_st8(td1 + c0 / 2, pk);
+                for (int g = 0; g < 2; ++g) {
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = ptx::pack_bf16(va[16 * g + 2 * i], va[16 * g + 2 * i + 1]);
+                    ptx::tmem_st8(td1 + c0 / 2 + 8 * g, pk);
+                }
             }
             ptx::tmem_wait_st();
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) { ptx::mbar_arrive(&d1_empty[ab]); ptx::mbar_arrive(&mid_full[ab]); }
             GN_T(t_e1 += clock64() - t2;)
+            if (it + 2 < n_it) epilogue0(it + 2);
         }
         GN_T(if (blockIdx.x == 0 && lane == 0 && (warp == 2 || warp == 9) && n_it > 0)
-                 printf("gn0 epilogue-1 warp %d: per board: wait d1_full %lld, mid_empty %lld, epi1 %lld\n",
-                        warp, w_d1f / n_it, w_me / n_it, t_e1 / n_it);)
+                 printf("gn0 epilogue-1/0 warp %d: per board: wait d1_full %lld, mid_empty %lld, epi1 %lld | wait de_full %lld, a_empty %lld, epi0 %lld\n",
+                        warp, w_d1f / n_it, w_me / n_it, t_e1 / n_it, e_w1 / n_it, e_w2 / n_it, e_work / n_it);)
     }
     ptx::tc_fence_before();
     __syncthreads();
