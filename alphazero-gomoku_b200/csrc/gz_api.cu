@@ -4,6 +4,7 @@
 // work launches kernels and fails with GZ_ERR_CUDA when there is no device.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <chrono>
@@ -1135,6 +1136,13 @@ extern "C" int gz_reset_counters(gz_handle h) {
 
 // ---- stage timing --------------------------------------------------------------------------------
 namespace gz {
+// Off by default: measured on bench config 3 (profiles/r02_pdl.md) the GraphNet stage of the event-profiled step drops
+// by 9 ms, but the timed step does not move (597.2 / 597.7 ms with it, 595.5 / 595.6 without): kernels already queue
+// back to back, and under the board's power cap an idle gap that is filled is paid back in clock.  GZ_PDL=1 enables it.
+bool pdl_enabled() {
+    static const bool on = getenv("GZ_PDL") && atoi(getenv("GZ_PDL")) != 0;
+    return on;
+}
 static cudaEvent_t next_event(Engine &e) {
     if (e.ev_used == e.ev_pool.size()) {
         cudaEvent_t ev;

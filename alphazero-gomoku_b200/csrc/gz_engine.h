@@ -29,6 +29,26 @@ constexpr int kHeadChunksP = 8, kHeadChunksV = 4;             // ceil(450 / 64),
 constexpr size_t kHeadTileBytesP = (size_t)kHeadChunksP * 2 * kHeadBlockBytes;
 constexpr size_t kHeadTileBytesV = (size_t)kHeadChunksV * 2 * kHeadBlockBytes;
 #if defined(__CUDACC__)
+// Programmatic dependent launch.  A kernel launched through launch_pdl may begin (barrier set-up, tensor-memory
+// allocation, weight loads) while the kernel before it in the stream is still running, and MUST call pdl_wait() before
+// it reads or writes anything that kernel touches: pdl_wait() returns once the whole preceding grid has completed and
+// its writes are visible.  pdl_trigger() in the preceding kernel lets the next grid's CTAs be scheduled as soon as all
+// of this grid's CTAs have started (they take an SM whenever its resources allow); without it they are scheduled when
+// this grid exits.  Both are no-ops for kernels launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();   // GZ_PDL=1 switches the attribute on (gz_api.cu: off by default, it measured no gain)
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
 __host__ __device__ __forceinline__ size_t head_operand_offset(int board, int k, int chunks) {   // of the hi value
     return ((size_t)(board >> 7) * chunks + (k >> 6)) * 2 * kHeadBlockBytes + ((k >> 3) & 7) * 2048 +
            (board & 127) * 16 + (k & 7) * 2;

@@ -17,6 +17,7 @@ __global__ void __launch_bounds__(128) k_planner_score(const gz_board *__restric
                                                        int k, int32_t *__restrict__ topk,
                                                        int32_t *__restrict__ ntop,
                                                        int64_t *__restrict__ scores2) {
+    pdl_trigger();   // the GraphNet kernel behind this one may set itself up while this grid drains (gz_engine.h)
     int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (g >= G) return;

@@ -99,6 +99,7 @@ __global__ void __launch_bounds__(128) k_tree_step(TreeArrays t, SimArrays sm, i
                                                    int n_log, const double *__restrict__ tanh_table,
                                                    int n_tanh,
                                                    unsigned long long *__restrict__ counters) {
+    pdl_trigger();   // the input convolution behind this kernel may set itself up while this grid drains (gz_engine.h)
     int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (g >= G) return;

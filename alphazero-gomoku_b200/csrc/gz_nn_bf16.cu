@@ -118,6 +118,10 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // programmatic dependent launch (gz_engine.h): everything above ran beside the tail of the kernel before this one;
+    // warp 0 still issues its weight loads first
+    pdl_trigger();
+    if (warp != 0) pdl_wait();
 
     if (warp == 0 && FROM_BOARD) {
         // ================= producer: one-hot slab from the bitboards =================
@@ -126,6 +130,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             ptx::mbar_expect_tx(&b_full[0], C::KSTEPS * C::WSTEP_BYTES);
             ptx::bulk_g2s(wbuf, w_packed, C::KSTEPS * C::WSTEP_BYTES, &b_full[0]);
         }
+        pdl_wait();
         // the next board's bitboards are fetched while this one is expanded (the loop is otherwise one global
         // load latency per board long)
         auto next_board = [&](int b) {
@@ -171,6 +176,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                     ptx::bulk_g2s(wbuf + ks * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES,
                                   C::WSTEP_BYTES, &b_full[0]);
             }
+            pdl_wait();
             uint32_t it = 0, wstage = 0, wphase = 0;
             for (int b = blockIdx.x; b < G; b += gridDim.x) {
                 if (active && !active[ph(b)]) continue;
@@ -760,12 +766,15 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
     // accumulator block of (buffer ab, M half h): 128 columns [D_a | D_b]
     auto acc_of = [&](int ab, int h) { return tmem_base + (uint32_t)(ab * 256 + h * 128); };
     auto board_of = [&](int it) { const int b = blockIdx.x + it * (int)gridDim.x; return rev ? G - 1 - b : b; };
+    pdl_trigger();                 // programmatic dependent launch (gz_engine.h); warp 0 issues its weight loads first
+    if (warp != 0) pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
             ptx::mbar_expect_tx(w_full, C::W3_BYTES + C::W1_BYTES);
             for (int t = 0; t < 9; ++t) ptx::bulk_g2s(sw3 + t * 8192, w3 + t * 8192, 8192, w_full);
             ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
+            pdl_wait();
             for (int it = 0; it < n_it; ++it) {
                 const int b = board_of(it), ab = it % NSLAB;
                 ptx::mbar_wait(&a_empty[ab], ((it / NSLAB) & 1) ^ 1);
@@ -1048,6 +1057,8 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
     const int n_it = blockIdx.x < G ? (G - 1 - blockIdx.x) / gridDim.x + 1 : 0;
     auto acc_of = [&](int ab, int h) { return tmem_base + (uint32_t)(ab * 256 + h * 128); };   // [D_a | D_b]
     auto board_of = [&](int it) { const int b = blockIdx.x + it * (int)gridDim.x; return rev ? G - 1 - b : b; };
+    pdl_trigger();                 // programmatic dependent launch (gz_engine.h); warp 0 issues its weight loads first
+    if (warp != 0) pdl_wait();
 
     if (warp == 0 || warp == 19) {
         // ================= im2col producers: M half hh = tile rows [128 hh, 128 hh + 128) =================
@@ -1058,6 +1069,7 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::bulk_g2s(sw1, w1, C::W1_BYTES, w_full);
             ptx::bulk_g2s(swe, we, C::WE_BYTES, w_full);
         }
+        if (warp == 0) pdl_wait();
         // every lane holds the whole position: 8 words per colour (one broadcast load each), fetched one board ahead
         auto load_words = [&](int it, uint4 *q) {
             if (it < n_it) {
@@ -1407,11 +1419,11 @@ static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *ou
     if (pairs) {
         const uint8_t *w3 = e.bw.gn_l3p_w[block];
         if (nslab == 3) {
-            if (head_out) k_gn_block_pairs<true, 3><<<grid, 352, GnPairsCfg<3>::SMEM, s>>>(in, w3, w1, kc, out, head_out, G, rev);
-            else k_gn_block_pairs<false, 3><<<grid, 352, GnPairsCfg<3>::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G, rev);
+            if (head_out) launch_pdl(k_gn_block_pairs<true, 3>, dim3(grid), dim3(352), GnPairsCfg<3>::SMEM, s, in, w3, w1, kc, out, head_out, G, rev);
+            else launch_pdl(k_gn_block_pairs<false, 3>, dim3(grid), dim3(352), GnPairsCfg<3>::SMEM, s, in, w3, w1, kc, out, (uint8_t *)nullptr, G, rev);
         } else {
-            if (head_out) k_gn_block_pairs<true, 2><<<grid, 352, GnPairsCfg<2>::SMEM, s>>>(in, w3, w1, kc, out, head_out, G, rev);
-            else k_gn_block_pairs<false, 2><<<grid, 352, GnPairsCfg<2>::SMEM, s>>>(in, w3, w1, kc, out, nullptr, G, rev);
+            if (head_out) launch_pdl(k_gn_block_pairs<true, 2>, dim3(grid), dim3(352), GnPairsCfg<2>::SMEM, s, in, w3, w1, kc, out, head_out, G, rev);
+            else launch_pdl(k_gn_block_pairs<false, 2>, dim3(grid), dim3(352), GnPairsCfg<2>::SMEM, s, in, w3, w1, kc, out, (uint8_t *)nullptr, G, rev);
         }
     } else {
         const uint8_t *w3 = e.bw.gn_l3_w[block];
@@ -1436,8 +1448,8 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
     static const int cap = getenv("GZ_CONV_GRID") ? atoi(getenv("GZ_CONV_GRID")) : 0;   // EXPERIMENT
     if (cap > 0 && grid > cap) grid = cap;
     static const bool alternate = !(getenv("GZ_GN_ALTERNATE") && atoi(getenv("GZ_GN_ALTERNATE")) == 0);   // A/B switch
-    kern<<<grid, 64 + 32 * conv_epi_warps<FROM_BOARD>(), C::SMEM, s>>>(in, w, bias, res, out, active, G, heads,
-                                                                       alternate ? rev : 0);
+    launch_pdl(kern, dim3(grid), dim3(64 + 32 * conv_epi_warps<FROM_BOARD>()), C::SMEM, s, in, w, bias, res, out, active, G,
+               heads, alternate ? rev : 0);
 }
 
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
@@ -1477,8 +1489,8 @@ void nn_graphnet_convs_bf16(Engine &e, const gz_board *boards, const uint8_t *ac
         memcpy(kc.head_w, w.gn_host_head, sizeof(float) * 130);
         memcpy(kc.be, w.gn_host_embed_bias, sizeof(float) * 64);
         const int grid = G < e.sm_count ? G : e.sm_count;
-        k_gn_block0_embed<<<grid, GnEmbedCfg::THREADS, GnEmbedCfg::SMEM, s>>>(boards, w.gn_embed_i2c_w, w.gn_l3p_w[0],
-                                                                              w.gn_l1_w[0], kc, p1, G, 0);
+        launch_pdl(k_gn_block0_embed, dim3(grid), dim3(GnEmbedCfg::THREADS), GnEmbedCfg::SMEM, s, boards,
+                   (const uint8_t *)w.gn_embed_i2c_w, (const uint8_t *)w.gn_l3p_w[0], (const uint8_t *)w.gn_l1_w[0], kc, p1, G, 0);
         for (int i = 1; i < 4; ++i)
             launch_gn_block(e, (i & 1) ? p1 : p0, i, (i & 1) ? p0 : p1, i == 3 ? e.gn_pc : nullptr, G, s, i & 1);
         prof_end(e, s);
