@@ -1,4 +1,5 @@
-"""Print the handful of ncu raw-page metrics the profile notes quote.  usage: ncu_key_metrics.py report.ncu-rep"""
+"""Print the handful of ncu raw-page metrics the profile notes quote.
+usage: ncu_key_metrics.py report.ncu-rep [--index N (N-th captured launch, default 0)] [--traffic STAGE]"""
 import csv, subprocess, sys
 
 WANT = [
@@ -15,7 +16,8 @@ WANT = [
 ]
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-head, units, vals = rows[0], rows[1], rows[2]
+IDX = int(sys.argv[sys.argv.index("--index") + 1]) if "--index" in sys.argv else 0
+head, units, vals = rows[0], rows[1], rows[2 + IDX]
 for n, u, v in zip(head, units, vals):
     if n == "Kernel Name": print(n, "=", v[:110])
     if n in WANT: print(f"{n} = {v} {u}")
