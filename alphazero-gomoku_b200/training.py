@@ -469,18 +469,32 @@ def main(iterations=6, games_per_iteration=10, device=None, models_dir="models",
                                  capturable=device.type == "cuda")   # capturable: train_epoch replays a CUDA graph
     scheduler = torch.optim.lr_scheduler.StepLR(optimizer, step_size=2, gamma=0.85)
     best_val, patience, patience_count, snapshot, history = math.inf, 3, 0, None, []
+    eval_games = int(kw.pop("eval_games", 6))
+    precision = kw.get("precision", "bf16")
     for it in range(1, iterations + 1):
+        # phases one and two; the evaluation comes after the best-model bookkeeping, as in training.py:478-503
         res = run_iteration(model, optimizer, scheduler, device, games_per_iteration=games_per_iteration,
-                            baseline=snapshot, seed=it, **kw)
+                            eval_games=0, seed=it, **kw)
         history.append(res)
+        if "val_loss" not in res:        # fewer than 8 samples: the reference `continue`s -- no checkpoint, no
+            continue                     # evaluation, patience untouched (training.py:431-433)
         model.save_model(os.path.join(models_dir, "alphazero_gomoku_iter_%d.pth" % it))
-        if res.get("val_loss", math.inf) < best_val:
+        if res["val_loss"] < best_val:
             best_val, patience_count = res["val_loss"], 0
             best_path = os.path.join(models_dir, "alphazero_gomoku_best.pth")
             model.save_model(best_path)
             snapshot = GomokuModel(model_path=best_path, board_size=15, device=str(device))
         else:
             patience_count += 1
+        # six evaluate_model(games=1) calls: the current model is black in every one of them (training.py:489-497)
+        model.eval_mode()
+        ev = {"wins": 0, "losses": 0, "draws": 0}
+        for eg in range(eval_games):
+            st = evaluate_model(model, snapshot, device, games=1, seed=1000 * it + eg, precision=precision)
+            for k in ev:
+                ev[k] += st.get(k, 0)
+        ev["win_rate"] = ev["wins"] / max(1, ev["wins"] + ev["losses"] + ev["draws"])
+        res["eval"] = ev
         print("iteration %d: %s" % (it, {k: v for k, v in res.items() if k != "selfplay_stats"}))
         if patience_count >= patience:
             break

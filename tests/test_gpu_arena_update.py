@@ -207,3 +207,20 @@ def test_graphed_update_matches_eager(weights):
     lg_, _, _, sg, ng = run("graphed", 1100, 2)
     assert se == sg == {18} and ne == ng == 18
     assert np.allclose(le, lg_, rtol=2e-3), (le, lg_)
+
+
+def test_training_main_follows_the_reference_iteration_order(tmp_path):
+    """training.main (training.py:361-537): per iteration self-play -> update -> iteration checkpoint -> best-model
+    bookkeeping -> evaluation as `eval_games` single-game calls against the snapshot taken AFTER this iteration's
+    update (iteration 1 therefore plays its own fresh snapshot, not the RandomAgent), final checkpoint at the end."""
+    import os
+    import training
+    hist = training.main(iterations=2, games_per_iteration=4, device="cuda", models_dir=str(tmp_path), difficulty="easy",
+                         num_simulations=8, planner_steps=1, epochs=1, batch_size=32, eval_games=2)
+    assert len(hist) == 2
+    for it, res in enumerate(hist, 1):
+        assert res["games"] == 4 and res["samples"] >= 8 and np.isfinite(res["val_loss"])
+        assert os.path.exists(tmp_path / ("alphazero_gomoku_iter_%d.pth" % it))
+        ev = res["eval"]
+        assert ev["wins"] + ev["losses"] + ev["draws"] == 2 and 0.0 <= ev["win_rate"] <= 1.0
+    assert os.path.exists(tmp_path / "alphazero_gomoku_best.pth") and os.path.exists(tmp_path / "alphazero_gomoku_final.pth")
