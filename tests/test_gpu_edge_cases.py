@@ -53,6 +53,34 @@ def test_ragged_batches_match_oracle(weights, oracle, G, precision):
     eng.close()
 
 
+@pytest.mark.parametrize("G", [1, 2, 147, 149, 300, 445])
+def test_planner_networks_on_ragged_batches(weights, G):
+    """k_gn_block0_embed / k_gn_block_pairs are persistent kernels of min(G, 148) CTAs whose per-CTA board count
+    decides which prologue and tail paths run (one board: no pipelining at all; two: both embeds in the prologue; three
+    and more: the steady state), and consecutive layers walk the boards in opposite directions.  For batch sizes that
+    give 1, 2, 3 and 4 boards per CTA (and mixes of them): bf16 GraphNet / DQN outputs within 2e-2 of the fp32 engine's
+    (relative to the logits' scale), and every board bit-identical to the same board evaluated in a batch of one."""
+    import engine
+    import workload
+    cells, tm, mc = workload.make_positions(G, seed=90 + G)
+    out = []
+    for prec in (0, 1):
+        e = engine.Engine(max_games=G, max_simulations=8, precision=prec)
+        e.set_pv_weights(weights["pv"])
+        e.set_planner_weights(weights["graphnet"], weights["dqn"])
+        b = e.boards_from_cells(cells, tm, mc)
+        gl, gp, q = (t.cpu().numpy() for t in e.planner_nets_forward(b))
+        if prec == 1:
+            for i in sorted({0, G // 2, G - 1}):
+                gl1, gp1, q1 = (t.cpu().numpy() for t in e.planner_nets_forward(b[i:i + 1].clone()))
+                assert np.array_equal(gl1[0], gl[i]) and np.array_equal(q1[0], q[i]), (G, i)
+        out.append((gl, gp, q))
+        e.close()
+    (gl0, gp0, q0), (gl1, gp1, q1) = out
+    assert np.max(np.abs(gl1 - gl0)) < 2e-2 * max(1.0, np.abs(gl0).max())
+    assert np.max(np.abs(gp1 - gp0)) < 2e-2 and np.max(np.abs(q1 - q0)) < 2e-2
+
+
 def test_terminal_full_and_nearly_full_roots(weights, oracle):
     import engine
     import workload
