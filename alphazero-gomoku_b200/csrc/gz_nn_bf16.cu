@@ -1445,8 +1445,6 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
         configured = true;
     }
     int grid = G < e.sm_count ? G : e.sm_count;
-    static const int cap = getenv("GZ_CONV_GRID") ? atoi(getenv("GZ_CONV_GRID")) : 0;   // EXPERIMENT
-    if (cap > 0 && grid > cap) grid = cap;
     static const bool alternate = !(getenv("GZ_GN_ALTERNATE") && atoi(getenv("GZ_GN_ALTERNATE")) == 0);   // A/B switch
     launch_pdl(kern, dim3(grid), dim3(64 + 32 * conv_epi_warps<FROM_BOARD>()), C::SMEM, s, in, w, bias, res, out, active, G,
                heads, alternate ? rev : 0);
