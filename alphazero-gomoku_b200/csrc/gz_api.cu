@@ -240,16 +240,19 @@ static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const fl
                     f2bf((float)((double)w[((size_t)co * 3 + ci) * 9 + tap] * scale));
         }
 }
-// GraphNet embed [64][3][3][3] as one im2col GEMM operand for k_gn_block0_embed: K = 27 padded to 32, in the order the
-// kernel's producer builds the one-hot tile in: k = 3 * (3 * plane + ky) + kx (plane = black / white / empty)
-// -> [4 k-groups][64 cout][8 k] bf16
-static void pack_embed_im2col_bf16(std::vector<uint16_t> &out, const float *w) {
+// An input convolution [cout][3][3][3] (+ BN) as ONE im2col GEMM operand (k_gn_block0_embed, k_pv_conv0_tower0): K = 27
+// padded to 32, in the order the kernels' producers build the one-hot tile in: k = 3 * (3 * plane + ky) + kx (plane =
+// black / white / empty) -> [4 k-groups][cout][8 k] bf16
+static void pack_conv0_im2col_bf16(std::vector<uint16_t> &out, const float *w, const float *bn, int cout) {
     size_t base = out.size();
-    out.resize(base + (size_t)4 * 64 * 8, 0);
+    out.resize(base + (size_t)4 * cout * 8, 0);
     for (int k = 0; k < 27; ++k) {
         const int plane = k / 9, ky = (k / 3) % 3, kx = k % 3;
-        for (int co = 0; co < 64; ++co)
-            out[base + ((size_t)(k >> 3) * 64 + co) * 8 + (k & 7)] = f2bf(w[((size_t)co * 3 + plane) * 9 + ky * 3 + kx]);
+        for (int co = 0; co < cout; ++co) {
+            double scale = bn ? (double)bn[co] / sqrt((double)bn[3 * cout + co] + 1e-5) : 1.0;
+            out[base + ((size_t)(k >> 3) * cout + co) * 8 + (k & 7)] =
+                f2bf((float)((double)w[((size_t)co * 3 + plane) * 9 + ky * 3 + kx] * scale));
+        }
     }
 }
 // linear weight [nout][nin] -> K-chunks of 64 inputs: [chunk][8 k-groups][256 n][8 k] bf16, zero padded
@@ -328,10 +331,13 @@ extern "C" int gz_set_pv_weights(gz_handle h, const float *f, int64_t n) {
         }
         size_t off0 = bf.size() * 2;
         pack_conv0_bf16(bf, f, f + 3456 + 128, 128);
+        size_t off_i2c = bf.size() * 2;
+        pack_conv0_im2col_bf16(bf, f, f + 3456 + 128, 128);
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.pv_blob);
         if (rc) return rc;
         for (int i = 0; i < 4; ++i) e->bw.pv_tower_w[i] = e->bw.pv_blob + off[i];
         e->bw.pv_conv0_w = e->bw.pv_blob + off0;
+        e->bw.pv_conv0_i2c_w = e->bw.pv_blob + off_i2c;
     }
     {   // head FCs for gz_nn_fc.cu: policy 450 -> 225 (8 chunks, N 256), value 225 -> 64 (4 chunks, N 64), bias [256]
         const float *q = f + 3456 + 128 + 512 + 2 * (2 * (147456 + 128) + 2 * 512);
@@ -403,7 +409,7 @@ extern "C" int gz_set_planner_weights(gz_handle h, const float *gnf, int64_t ngn
         size_t off0 = bf.size() * 2;
         pack_conv0_bf16(bf, gnf, nullptr, 64);
         size_t off_i2c = bf.size() * 2;
-        pack_embed_im2col_bf16(bf, gnf);
+        pack_conv0_im2col_bf16(bf, gnf, nullptr, 64);
         memcpy(e->bw.gn_host_embed_bias, &pk.host[o[1]], 64 * sizeof(float));
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.gn_blob);
         if (rc) return rc;
