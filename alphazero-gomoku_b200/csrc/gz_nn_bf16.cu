@@ -1558,7 +1558,7 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
                 const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
                 if (ks == 6 && bn < G) {
                     // the next board's input convolution goes into the other accumulator buffer: free once the main
-                    // epilogue of board it - 1 has read it (a third of the way into this board at the latest)
+                    // epilogue of board it - 1 has read it (issued later, at K step 10, measured no better)
                     if (it >= 1) ptx::mbar_wait(&acc_empty[ab ^ 1], ((it - 1) >> 1) & 1);
                     ptx::tc_fence_after();
                     issue_conv0(it + 1);
