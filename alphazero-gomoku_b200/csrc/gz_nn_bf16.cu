@@ -66,11 +66,19 @@ __device__ __forceinline__ void store_head_operand(uint8_t *tile_base, int board
 
 // Epilogue warps: 4 (each does both halves of the board) when the 144 UMMAs of a 128 -> 128 layer hide the
 // epilogue anyway; 8 (one half each) for the 3 -> C input convolutions, whose 18 UMMAs per board leave the
-// kernel waiting for TMEM loads and stores (3.4 TB/s of output with 4 warps).
-template <bool FROM_BOARD> __host__ __device__ constexpr int conv_epi_warps() { return FROM_BOARD ? 8 : 4; }
+// kernel waiting for TMEM loads and stores (3.4 TB/s of output with 4 warps), and for the layers with a skip
+// connection: with 4 warps their epilogue took 12.1 k cycles per board against 9.2 k of UMMAs, and the issuer sat
+// 2.9 k cycles per board waiting for a free accumulator (scratch/conv_timing.py).
+template <bool FROM_BOARD, bool RESIDUAL> __host__ __device__ constexpr int conv_epi_warps() { return FROM_BOARD || RESIDUAL ? 8 : 4; }
 
+// -DGZ_CONV_TIMING: block 0 of the 128 -> 128 layers prints where its issuer and epilogue warps wait (scratch/conv_timing.py)
+#ifdef GZ_CONV_TIMING
+#define CV_T(...) __VA_ARGS__
+#else
+#define CV_T(...)
+#endif
 template <int CIN, int COUT, int TAPS, bool RESIDENT, bool RESIDUAL, bool FROM_BOARD = false, bool HEADS = false>
-__global__ void __launch_bounds__(64 + 32 * conv_epi_warps<FROM_BOARD>(), 1)
+__global__ void __launch_bounds__(64 + 32 * conv_epi_warps<FROM_BOARD, RESIDUAL>(), 1)
 k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w_packed,
             const float *__restrict__ bias, const uint8_t *__restrict__ res_planes,
             uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G, HeadConv heads, int rev) {
@@ -99,7 +107,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             ptx::mbar_init(&a_full[i], 1);
             ptx::mbar_init(&a_empty[i], 1);
             ptx::mbar_init(&acc_full[i], 1);
-            ptx::mbar_init(&acc_empty[i], conv_epi_warps<FROM_BOARD>());
+            ptx::mbar_init(&acc_empty[i], conv_epi_warps<FROM_BOARD, RESIDUAL>());
         }
         for (int i = 0; i < 4; ++i) {
             ptx::mbar_init(&b_full[i], 1);
@@ -207,12 +215,16 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = COUT * 16;
             if (RESIDENT) ptx::mbar_wait(&b_full[0], 0);
             uint32_t it = 0, wstage = 0, wphase = 0;
+            CV_T(const long long tk0 = clock64(); long long w_acc = 0, w_a = 0, w_b = 0;)
             for (int b = blockIdx.x; b < G; b += gridDim.x) {
                 if (active && !active[ph(b)]) continue;
                 const int ab = it & 1;
                 const uint32_t par = (it >> 1) & 1;
+                CV_T(const long long t0 = clock64();)
                 ptx::mbar_wait(&acc_empty[ab], par ^ 1);
+                CV_T(const long long t1 = clock64(); w_acc += t1 - t0;)
                 ptx::mbar_wait(&a_full[ab], par);
+                CV_T(w_a += clock64() - t1;)
                 ptx::tc_fence_after();
                 // one base descriptor per operand; everything else is a compile-time constant added to the
                 // 16-byte address field (K-step loop fully unrolled)
@@ -227,7 +239,9 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                     if (RESIDENT) {
                         db0 = ptx::make_desc(ptx::smem_u32(wbuf) + ks * C::WSTEP_BYTES, LBO_B, 128);
                     } else {
+                        CV_T(const long long t2 = clock64();)
                         ptx::mbar_wait(&b_full[wstage], wphase);
+                        CV_T(w_b += clock64() - t2;)
                         ptx::tc_fence_after();
                         db0 = ptx::make_desc(ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES), LBO_B, 128);
                     }
@@ -248,6 +262,9 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                 ptx::umma_commit_elect(&acc_full[ab]);
                 ++it;
             }
+            CV_T(if (blockIdx.x == 0 && lane == 0 && it > 0 && CIN == 128)
+                     printf("conv issuer (res %d heads %d): %u boards, total %lld | per board: wait acc_empty %lld, a_full %lld, b_full (18 waits) %lld\n",
+                            (int)RESIDUAL, (int)HEADS, it, clock64() - tk0, w_acc / it, w_a / it, w_b / it);)
         }
     } else {
         // ================= epilogue (warps 2..5) =================
@@ -256,7 +273,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
         // behind the MMAs instead of stalling every 16-channel step.
         const int q = warp & 3;                 // TMEM lane quadrant this warp may read
         constexpr int NCG = COUT / 8;
-        uint4 res[2][RESIDUAL ? NCG : 1];
+        uint4 res[conv_epi_warps<FROM_BOARD, RESIDUAL>() == 8 ? 1 : 2][RESIDUAL ? NCG : 1];
         auto fetch_res = [&](int bl, int h, uint4 *r) {
             const int b = ph(bl);
             const uint8_t *src = res_planes + kGuardBytes + (size_t)b * NCG * kPlaneBytes +
@@ -339,15 +356,22 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             return b;
         };
         uint32_t it = 0;
+        CV_T(long long e_wait = 0, e_work = 0;)
         int b = blockIdx.x < G && active && !active[ph(blockIdx.x)] ? next_board(blockIdx.x) : blockIdx.x;
-        if (RESIDUAL && b < G) fetch_res(b, 0, res[0]);
+        constexpr bool kEight = conv_epi_warps<FROM_BOARD, RESIDUAL>() == 8;
+        const int my_h = (warp - 2) >> 2;       // kEight: the M half of this warp
+        if (RESIDUAL && b < G) fetch_res(b, kEight ? my_h : 0, res[0]);
         while (b < G) {
             const int ab = it & 1;
             const int bn = next_board(b);
+            CV_T(const long long t0 = clock64();)
             ptx::mbar_wait(&acc_full[ab], (it >> 1) & 1);
+            CV_T(const long long t1 = clock64(); e_wait += t1 - t0;)
             ptx::tc_fence_after();
-            if (conv_epi_warps<FROM_BOARD>() == 8) {
-                half(b, ab, (warp - 2) >> 2, res[0]);        // FROM_BOARD layers have no residual
+            if constexpr (kEight) {
+                half(b, ab, my_h, res[0]);
+                // the next board's skip tensor for this half: its latency hides behind that board's UMMAs
+                if (RESIDUAL && bn < G) fetch_res(bn, my_h, res[0]);
             } else {
                 if (RESIDUAL) fetch_res(b, 1, res[1]);
                 half(b, ab, 0, res[0]);
@@ -357,9 +381,12 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[ab]);
+            CV_T(e_work += clock64() - t1;)
             ++it;
             b = bn;
         }
+        CV_T(if (blockIdx.x == 0 && lane == 0 && warp == 2 && it > 0 && CIN == 128)
+                 printf("conv epilogue (res %d heads %d): per board: wait acc_full %lld, work %lld\n", (int)RESIDUAL, (int)HEADS, e_wait / it, e_work / it);)
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -1710,7 +1737,7 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
     }
     int grid = G < e.sm_count ? G : e.sm_count;
     static const bool alternate = !(getenv("GZ_GN_ALTERNATE") && atoi(getenv("GZ_GN_ALTERNATE")) == 0);   // A/B switch
-    launch_pdl(kern, dim3(grid), dim3(64 + 32 * conv_epi_warps<FROM_BOARD>()), C::SMEM, s, in, w, bias, res, out, active, G,
+    launch_pdl(kern, dim3(grid), dim3(64 + 32 * conv_epi_warps<FROM_BOARD, RESIDUAL>()), C::SMEM, s, in, w, bias, res, out, active, G,
                heads, alternate ? rev : 0);
 }
 

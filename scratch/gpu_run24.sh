@@ -1,0 +1,6 @@
+#!/bin/bash
+timeout 300 python -m pytest tests/test_gpu_bf16.py tests/test_gpu_edge_cases.py tests/test_gpu_timed_path.py -q -x -k "not outcome_rates and not fp32_bit_exact" > gpurun_out/r02z_pytest.log 2>&1; tail -2 gpurun_out/r02z_pytest.log
+timeout 200 python scratch/conv_timing.py 2>&1 | grep -E "conv (issuer|epilogue)" | tail -8
+timeout 200 python bench.py --steps 4 --warmup 3 --selfplay-plies 0 --s400-steps 0 --cpu-seconds 1 --port-only > gpurun_out/r02z.json 2> gpurun_out/r02z.err
+python -c "
+import json; d=json.loads(open('gpurun_out/r02z.json').read().strip().splitlines()[-1]); print(round(d['value']), round(d['ms_per_step'],1), d['roofline']['stage_ms'], d['clocks']['sm_mhz'])"
