@@ -36,10 +36,22 @@ struct ConvCfg {
     static constexpr int SLAB_ROWS = TAPS == 9 ? 290 : 256;  // positions [-1,289) or [16,272)
     static constexpr int SLAB_BYTES = CG * SLAB_ROWS * 16;
     static constexpr int WSTEP_BYTES = (KSTEP / 8) * COUT * 16;   // one K-step of weights: [cg][COUT][8]
-    static constexpr int NSTAGE = RESIDENT ? KSTEPS : 4;
+    // HALVES (the 128-channel streaming layers): the K steps run chunk-major -- nine taps on channels 0-63, then nine on
+    // 64-127 -- so the input lives in THREE half slabs of 64 channels (a board's first half is free for the next board
+    // after nine K steps) instead of two whole ones, and the 37 KB that frees pays for a weight ring of six 16 KB stages
+    // instead of four.  The ring is what paces these layers: the issuer waited 3.5-4 k cycles per board for weights
+    // (~220 per K step: a refill from L2 takes ~1800 cycles under load, three full stages cover 1536).
+#ifdef GZ_CONV_NO_HALVES      // A/B build (scratch/ab_lib.py): two whole slabs, four weight stages
+    static constexpr bool HALVES = false;
+#else
+    static constexpr bool HALVES = !RESIDENT && CHUNKS == 2 && TAPS == 9;
+#endif
+    static constexpr int HALF_BYTES = SLAB_BYTES / 2;
+    static constexpr int A_BYTES = HALVES ? 3 * HALF_BYTES : 2 * SLAB_BYTES;
+    static constexpr int NSTAGE = RESIDENT ? KSTEPS : HALVES ? 6 : 4;
     static constexpr int W_BYTES = NSTAGE * WSTEP_BYTES;
     static constexpr int TCOLS = 4 * COUT;                   // 2 buffers x 2 halves x COUT fp32 columns
-    static constexpr int SMEM = 2 * SLAB_BYTES + W_BYTES + COUT * 4 + 256 + 128 + (3 * COUT + 4) * 4;
+    static constexpr int SMEM = A_BYTES + W_BYTES + COUT * 4 + 256 + 128 + (3 * COUT + 4) * 4;
 };
 
 // FROM_BOARD: the input is the board itself (CIN = 16: channel 0 black, 1 white, 2 empty, the rest
@@ -84,13 +96,14 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             uint8_t *__restrict__ out_planes, const uint8_t *__restrict__ active, int G, HeadConv heads, int rev) {
     using C = ConvCfg<CIN, COUT, TAPS, RESIDENT>;
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *slab = smem;                                   // [2][SLAB_BYTES]
-    uint8_t *wbuf = smem + 2 * C::SLAB_BYTES;               // [NSTAGE][WSTEP_BYTES]
+    uint8_t *slab = smem;                                   // [2][SLAB_BYTES], or [3][HALF_BYTES] (C::HALVES)
+    uint8_t *wbuf = smem + C::A_BYTES;                      // [NSTAGE][WSTEP_BYTES]
     float *sbias = reinterpret_cast<float *>(wbuf + C::W_BYTES);
     uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(sbias) + COUT * 4);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *acc_full = bars + 4, *acc_empty = bars + 6;
-    uint64_t *b_full = bars + 8, *b_empty = bars + 8 + 4;   // ring (streaming) or b_full[0] = "resident loaded"
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16 + 2);
+    uint64_t *a_full = bars, *a_empty = bars + 3, *acc_full = bars + 6, *acc_empty = bars + 8;
+    uint64_t *b_full = bars + 10, *b_empty = bars + 16;     // ring (streaming) or b_full[0] = "resident loaded"
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 22);
+    static_assert(C::NSTAGE <= 6 || RESIDENT, "barrier slots");
     float *s_hw = reinterpret_cast<float *>(bars + 32);     // HEADS: [COUT][2] policy, [COUT] value, 3 biases
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
@@ -103,13 +116,15 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
         if (threadIdx.x == 0) { s_hw[3 * COUT] = heads.pb[0]; s_hw[3 * COUT + 1] = heads.pb[1]; s_hw[3 * COUT + 2] = heads.vb[0]; }
     }
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 3; ++i) {
             ptx::mbar_init(&a_full[i], 1);
             ptx::mbar_init(&a_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&acc_full[i], 1);
             ptx::mbar_init(&acc_empty[i], conv_epi_warps<FROM_BOARD, RESIDUAL>());
         }
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < 6; ++i) {
             ptx::mbar_init(&b_full[i], 1);
             ptx::mbar_init(&b_empty[i], 1);
         }
@@ -186,26 +201,81 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
             }
             pdl_wait();
             uint32_t it = 0, wstage = 0, wphase = 0;
-            for (int b = blockIdx.x; b < G; b += gridDim.x) {
-                if (active && !active[ph(b)]) continue;
-                const int ab = it & 1;
-                ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
-                ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
+            auto next_board = [&](int b) {
+                for (b += gridDim.x; b < G && active && !active[ph(b)]; b += gridDim.x) {}
+                return b;
+            };
+            // slab of the n-th board of this CTA: channel groups [cg0, cg1)
+            auto load_slab = [&](int b, uint32_t n, int cg0, int cg1) {
+                const int ab = n & 1;
+                if (cg0 == 0) {
+                    ptx::mbar_wait(&a_empty[ab], ((n >> 1) & 1) ^ 1);
+                    ptx::mbar_expect_tx(&a_full[ab], C::SLAB_BYTES);
+                }
                 const uint8_t *src = in_planes + kGuardBytes + (size_t)ph(b) * C::CG * kPlaneBytes +
                                      (TAPS == 9 ? -16 : 256);
-                for (int cg = 0; cg < C::CG; ++cg)
+                for (int cg = cg0; cg < cg1; ++cg)
                     ptx::bulk_g2s(slab + ab * C::SLAB_BYTES + cg * C::SLAB_ROWS * 16,
                                   src + (size_t)cg * kPlaneBytes, C::SLAB_ROWS * 16, &a_full[ab]);
-                if (!RESIDENT) {
-                    for (int ks = 0; ks < C::KSTEPS; ++ks) {
+            };
+            // C::HALVES: channel group cg of half slab number j = 2 * (board number) + chunk, ring of three
+            auto load_half = [&](int b, uint32_t j, int cg) {
+                const uint32_t hb = j % 3;
+                if (cg == 0) {
+                    ptx::mbar_wait(&a_empty[hb], ((j / 3) & 1) ^ 1);
+                    ptx::mbar_expect_tx(&a_full[hb], C::HALF_BYTES);
+                }
+                const uint8_t *src = in_planes + kGuardBytes + ((size_t)ph(b) * C::CG + (j & 1) * 8 + cg) * kPlaneBytes - 16;
+                ptx::bulk_g2s(slab + hb * C::HALF_BYTES + cg * C::SLAB_ROWS * 16, src, C::SLAB_ROWS * 16, &a_full[hb]);
+            };
+            int b = blockIdx.x < G && active && !active[ph(blockIdx.x)] ? next_board(blockIdx.x) : blockIdx.x;
+            if constexpr (C::HALVES) {
+                if (b < G)
+                    for (int cg = 0; cg < 8; ++cg) load_half(b, 0, cg);
+                while (b < G) {
+                    const int bn = next_board(b);
+                    // weight steps in chunk-major order; along with them, one 4.6 KB channel group per step, this board's
+                    // second half slab (steps 0-7: needed from step 9) and the next board's first (steps 8-15).  Both ring
+                    // slots are free by then (the producer runs at most six steps ahead of the UMMAs), so the weight
+                    // stream never waits for them; a 37 KB or 74 KB request in one piece delays the weight ring instead.
+                    for (int kk = 0; kk < C::KSTEPS; ++kk) {
+                        if (kk < 8) load_half(b, 2 * it + 1, kk);
+                        else if (kk < 16 && bn < G) load_half(bn, 2 * it + 2, kk - 8);
+                        const int ks = (kk % 9) * 2 + kk / 9;           // packed order is tap-major
                         ptx::mbar_wait(&b_empty[wstage], wphase ^ 1);
                         ptx::mbar_expect_tx(&b_full[wstage], C::WSTEP_BYTES);
                         ptx::bulk_g2s(wbuf + wstage * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES,
                                       C::WSTEP_BYTES, &b_full[wstage]);
-                        if (++wstage == 4) { wstage = 0; wphase ^= 1; }
+                        if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
+                    }
+                    ++it;
+                    b = bn;
+                }
+            } else {
+            if (b < G) load_slab(b, 0, 0, C::CG);
+            while (b < G) {
+                const int bn = next_board(b);
+                if (RESIDENT) {
+                    if (bn < G) load_slab(bn, it + 1, 0, C::CG);
+                } else {
+                    static_assert(RESIDENT || C::CG <= C::KSTEPS, "one channel group of the next slab per weight step");
+                    for (int ks = 0; ks < C::KSTEPS; ++ks) {
+                        // The next board's slab rides along with this board's weight stream, one channel group (4.6 KB)
+                        // per 16 KB weight step.  Requested behind the 18 weight steps it arrived ~1000 cycles late on
+                        // every board; requested in one piece early in the board its 74 KB delayed the weight ring,
+                        // which is the latency-critical stream (b_full waits 4.0 k -> 6.4 k cycles per board;
+                        // scratch/conv_timing.py).
+                        if (bn < G && ks < C::CG) load_slab(bn, it + 1, ks, ks + 1);
+                        ptx::mbar_wait(&b_empty[wstage], wphase ^ 1);
+                        ptx::mbar_expect_tx(&b_full[wstage], C::WSTEP_BYTES);
+                        ptx::bulk_g2s(wbuf + wstage * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES,
+                                      C::WSTEP_BYTES, &b_full[wstage]);
+                        if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
                     }
                 }
                 ++it;
+                b = bn;
+            }
             }
         }
     } else if (warp == 1) {
@@ -223,13 +293,48 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                 CV_T(const long long t0 = clock64();)
                 ptx::mbar_wait(&acc_empty[ab], par ^ 1);
                 CV_T(const long long t1 = clock64(); w_acc += t1 - t0;)
-                ptx::mbar_wait(&a_full[ab], par);
+                if constexpr (C::HALVES) ptx::mbar_wait(&a_full[(2 * it) % 3], ((2 * it) / 3) & 1);
+                else ptx::mbar_wait(&a_full[ab], par);
                 CV_T(w_a += clock64() - t1;)
                 ptx::tc_fence_after();
                 // one base descriptor per operand; everything else is a compile-time constant added to the
                 // 16-byte address field (K-step loop fully unrolled)
-                const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
                 const uint32_t acc = tmem_base + ab * 2 * COUT;
+                if constexpr (C::HALVES) {
+#pragma unroll
+                    for (int kk = 0; kk < C::KSTEPS; ++kk) {
+                        const int chunk = kk / 9, tap = kk - 9 * chunk;
+                        const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
+                        const uint32_t j = 2 * it + chunk, hb = j % 3;
+                        if (tap == 0 && chunk == 1) {
+                            CV_T(const long long t3 = clock64();)
+                            ptx::mbar_wait(&a_full[hb], (j / 3) & 1);
+                            CV_T(w_a += clock64() - t3;)
+                            ptx::tc_fence_after();
+                        }
+                        const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + hb * C::HALF_BYTES), LBO_A, 128);
+                        CV_T(const long long t2 = clock64();)
+                        ptx::mbar_wait(&b_full[wstage], wphase);
+                        CV_T(w_b += clock64() - t2;)
+                        ptx::tc_fence_after();
+                        const uint64_t db0 = ptx::make_desc(ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES), LBO_B, 128);
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                            for (int k = 0; k < C::KK; ++k)
+                                ptx::umma_bf16_elect(acc + h * COUT,
+                                                     da0 + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff + 128 * h),
+                                                     db0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, (kk | k) != 0);
+                        }
+                        ptx::umma_commit_elect(&b_empty[wstage]);
+                        if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
+                        if (tap == 8) ptx::umma_commit_elect(&a_empty[hb]);
+                    }
+                    ptx::umma_commit_elect(&acc_full[ab]);
+                    ++it;
+                    continue;
+                }
+                const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
 #pragma unroll
                 for (int ks = 0; ks < C::KSTEPS; ++ks) {
                     const int tap = ks / C::CHUNKS, chunk = ks - tap * C::CHUNKS;
@@ -255,7 +360,7 @@ k_conv_umma(const uint8_t *__restrict__ in_planes, const uint8_t *__restrict__ w
                     }
                     if (!RESIDENT) {
                         ptx::umma_commit_elect(&b_empty[wstage]);
-                        if (++wstage == 4) { wstage = 0; wphase ^= 1; }
+                        if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
                     }
                 }
                 ptx::umma_commit_elect(&a_empty[ab]);
