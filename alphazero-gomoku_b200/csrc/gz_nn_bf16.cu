@@ -1545,16 +1545,18 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
 // one-hot tile, ONE K = 32 GEMM (2 N = 128 UMMAs per M half) puts the 128-channel result into the accumulator buffer
 // the board is going to use -- idle between the main epilogue of board it - 2 and the board's own first tap --, eight
 // epilogue-0 warps apply bias + ReLU and write bf16 into the 3x3's input slab in shared memory; the 144 tap UMMAs and
-// the main epilogue are k_conv_umma<128, 128, 9>'s.  Weights stream through a 3-stage ring (the tile takes the 4th).
+// the main epilogue are k_conv_umma<128, 128, 9>'s (half slabs, chunk-major K order).  Weights stream through a 5-stage
+// ring (the im2col tile and its weights take the sixth stage's shared memory).
 //   warp 0      weight ring producer          warp 1       tcgen05.mma issuer (both M halves)
 //   warps 2-5   main epilogue (bias, ReLU, bf16 planes to HBM)
 //   warps 6-13  epilogue 0: quadrant = warp & 3, M half = (warp - 6) >> 2        warps 14, 15  im2col producers
 struct PvFusedCfg {
     static constexpr int CG = 16, SLAB_ROWS = 290, SLAB_BYTES = CG * SLAB_ROWS * 16;
-    static constexpr int KSTEPS = 18, WSTEP_BYTES = 8 * 128 * 16, NSTAGE = 3;
+    static constexpr int HALF_BYTES = SLAB_BYTES / 2;       // three half slabs of 64 channels, K steps chunk-major (ConvCfg::HALVES)
+    static constexpr int KSTEPS = 18, WSTEP_BYTES = 8 * 128 * 16, NSTAGE = 5;
     static constexpr int I2C_BYTES = 4 * 256 * 16, WE_BYTES = 4 * 128 * 16;
     static constexpr int THREADS = 512;
-    static constexpr int SMEM = 2 * SLAB_BYTES + NSTAGE * WSTEP_BYTES + I2C_BYTES + WE_BYTES + 2 * 128 * 4 + 512;
+    static constexpr int SMEM = 3 * HALF_BYTES + NSTAGE * WSTEP_BYTES + I2C_BYTES + WE_BYTES + 2 * 128 * 4 + 512;
 };
 
 __global__ void __launch_bounds__(PvFusedCfg::THREADS, 1)
@@ -1565,17 +1567,17 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
     using C = PvFusedCfg;
     constexpr int COUT = 128;
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *slab = smem;                                   // [2][SLAB_BYTES]
-    uint8_t *wbuf = slab + 2 * C::SLAB_BYTES;               // [NSTAGE][WSTEP_BYTES]
+    uint8_t *slab = smem;                                   // [3][HALF_BYTES]: half slab number j = 2 * board + chunk in slot j % 3
+    uint8_t *wbuf = slab + 3 * C::HALF_BYTES;               // [NSTAGE][WSTEP_BYTES]
     uint8_t *i2c = wbuf + C::NSTAGE * C::WSTEP_BYTES;       // one tile (the embed kernel has two: this one is over budget)
     uint8_t *swe = i2c + C::I2C_BYTES;
     float *sbias = reinterpret_cast<float *>(swe + C::WE_BYTES);
     float *sbias0 = sbias + COUT;
     uint64_t *bars = reinterpret_cast<uint64_t *>(sbias0 + COUT);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *acc_full = bars + 4, *acc_empty = bars + 6;
-    uint64_t *b_full = bars + 8, *b_empty = bars + 12;
-    uint64_t *e_full = bars + 16, *e_empty = bars + 17, *de_full = bars + 18, *we_full = bars + 20;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 21);
+    uint64_t *a_full = bars, *a_empty = bars + 3, *acc_full = bars + 6, *acc_empty = bars + 8;
+    uint64_t *b_full = bars + 10, *b_empty = bars + 16;
+    uint64_t *e_full = bars + 22, *e_empty = bars + 23, *de_full = bars + 24, *we_full = bars + 26;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 27);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
     auto ph = [&](int b) { return rev ? G - 1 - b : b; };
@@ -1588,9 +1590,11 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
         return b < G && active && !active[ph(b)] ? next_board(b) : b;
     };
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&a_full[i], 8);      // slab: written by the 8 epilogue-0 warps
+        for (int i = 0; i < 3; ++i) {
+            ptx::mbar_init(&a_full[i], 8);      // half slab: written by the 8 epilogue-0 warps
             ptx::mbar_init(&a_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&acc_full[i], 1);
             ptx::mbar_init(&acc_empty[i], 4);
             ptx::mbar_init(&de_full[i], 1);
@@ -1603,7 +1607,7 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
     }
     for (int i = threadIdx.x; i < COUT; i += C::THREADS) { sbias[i] = bias[i]; sbias0[i] = bias0[i]; }
     // the slab rows outside the board (and everything epilogue 0 never writes) stay zero for the whole kernel
-    for (int i = threadIdx.x; i < 2 * C::SLAB_BYTES / 16; i += C::THREADS)
+    for (int i = threadIdx.x; i < 3 * C::HALF_BYTES / 16; i += C::THREADS)
         reinterpret_cast<uint4 *>(slab)[i] = make_uint4(0u, 0u, 0u, 0u);
     ptx::fence_proxy_async();
     if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
@@ -1619,7 +1623,8 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::bulk_g2s(swe, we, C::WE_BYTES, we_full);
             uint32_t wstage = 0, wphase = 0;
             for (int b = first_board(); b < G; b = next_board(b)) {
-                for (int ks = 0; ks < C::KSTEPS; ++ks) {
+                for (int kk = 0; kk < C::KSTEPS; ++kk) {
+                    const int ks = (kk % 9) * 2 + kk / 9;       // chunk-major order; the pack is tap-major
                     ptx::mbar_wait(&b_empty[wstage], wphase ^ 1);
                     ptx::mbar_expect_tx(&b_full[wstage], C::WSTEP_BYTES);
                     ptx::bulk_g2s(wbuf + wstage * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES, C::WSTEP_BYTES,
@@ -1680,21 +1685,25 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
         while (b < G) {
             const int bn = next_board(b);
             const int ab = it & 1;
-            ptx::mbar_wait(&a_full[ab], (it >> 1) & 1);       // slab written by epilogue 0, which has also left the accumulator
-            ptx::tc_fence_after();
-            const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + ab * C::SLAB_BYTES), LBO_A, 128);
             const uint32_t acc = tmem_base + ab * 2 * COUT;
 #pragma unroll
-            for (int ks = 0; ks < C::KSTEPS; ++ks) {
-                const int tap = ks / 2, chunk = ks - tap * 2;
+            for (int kk = 0; kk < C::KSTEPS; ++kk) {
+                const int chunk = kk / 9, tap = kk - 9 * chunk;
                 const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
-                if (ks == 6 && bn < G) {
-                    // the next board's input convolution goes into the other accumulator buffer: free once the main
-                    // epilogue of board it - 1 has read it (issued later, at K step 10, measured no better)
+                const uint32_t j = 2 * it + chunk, hb = j % 3;
+                if (tap == 0) {      // half slab written by epilogue 0 (which has then also left the accumulator)
+                    ptx::mbar_wait(&a_full[hb], (j / 3) & 1);
+                    ptx::tc_fence_after();
+                }
+                if (kk == 10 && bn < G) {
+                    // the next board's input convolution goes into the other accumulator buffer, free once the main
+                    // epilogue of board it - 1 has read it; its epilogue 0 needs the half slab this board's first nine
+                    // K steps have just released (and the third one), so it is issued right behind them
                     if (it >= 1) ptx::mbar_wait(&acc_empty[ab ^ 1], ((it - 1) >> 1) & 1);
                     ptx::tc_fence_after();
                     issue_conv0(it + 1);
                 }
+                const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + hb * C::HALF_BYTES), LBO_A, 128);
                 ptx::mbar_wait(&b_full[wstage], wphase);
                 ptx::tc_fence_after();
                 const uint64_t db0 = ptx::make_desc(ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES), LBO_B, 128);
@@ -1702,14 +1711,13 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
                 for (int h = 0; h < 2; ++h) {
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        ptx::umma_bf16_elect(acc + h * COUT,
-                                             da0 + (uint64_t)((chunk * 8 + 2 * k) * C::SLAB_ROWS + rowoff + 128 * h),
-                                             db0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, (ks | k) != 0);
+                        ptx::umma_bf16_elect(acc + h * COUT, da0 + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff + 128 * h),
+                                             db0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, (kk | k) != 0);
                 }
                 ptx::umma_commit_elect(&b_empty[wstage]);
                 if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
+                if (tap == 8) ptx::umma_commit_elect(&a_empty[hb]);
             }
-            ptx::umma_commit_elect(&a_empty[ab]);
             ptx::umma_commit_elect(&acc_full[ab]);
             ++it;
             b = bn;
@@ -1723,10 +1731,13 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
         uint32_t it = 0;
         for (int b = first_board(); b < G; b = next_board(b), ++it) {
             const int ab = it & 1;
+            const uint32_t j0 = 2 * it, j1 = 2 * it + 1;
             ptx::mbar_wait(&de_full[ab], (it >> 1) & 1);
-            ptx::mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);        // the taps of board it - 2 have read this slab
+            ptx::mbar_wait(&a_empty[j0 % 3], ((j0 / 3) & 1) ^ 1);     // the UMMAs that read these two ring slots are done
+            ptx::mbar_wait(&a_empty[j1 % 3], ((j1 / 3) & 1) ^ 1);
             ptx::tc_fence_after();
-            uint8_t *dst = slab + ab * C::SLAB_BYTES + (size_t)(pos + 1) * 16;
+            uint8_t *dst0 = slab + (j0 % 3) * C::HALF_BYTES + (size_t)(pos + 1) * 16;      // channels 0-63
+            uint8_t *dst1 = slab + (j1 % 3) * C::HALF_BYTES + (size_t)(pos + 1) * 16;      // channels 64-127
             // the planes also go to HBM: they are the skip tensor of the first residual block (neural_network.py:139-141)
             uint8_t *gdst = conv0_planes + kGuardBytes + (size_t)ph(b) * (COUT / 8) * kPlaneBytes + (size_t)pos * 16;
 #pragma unroll
@@ -1740,7 +1751,7 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
                     for (int i = 0; i < 4; ++i)
                         pk[i] = valid ? ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + sbias0[c64 + c0 + 2 * i], 0.f),
                                                        fmaxf(v[c0 + 2 * i + 1] + sbias0[c64 + c0 + 2 * i + 1], 0.f)) : 0u;
-                    *reinterpret_cast<uint4 *>(dst + (size_t)((c64 + c0) / 8) * C::SLAB_ROWS * 16) =
+                    *reinterpret_cast<uint4 *>((c64 ? dst1 : dst0) + (size_t)(c0 / 8) * C::SLAB_ROWS * 16) =
                         make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4 *>(gdst + (size_t)((c64 + c0) / 8) * kPlaneBytes) =
                         make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -1749,7 +1760,7 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::fence_proxy_async();
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&a_full[ab]);
+            if (lane == 0) { ptx::mbar_arrive(&a_full[j0 % 3]); ptx::mbar_arrive(&a_full[j1 % 3]); }
         }
     } else {
         // ================= main epilogue (warps 2-5, both M halves each): bias, ReLU, bf16 planes =================
