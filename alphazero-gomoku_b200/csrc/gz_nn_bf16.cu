@@ -1666,8 +1666,11 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
         const uint64_t dwe0 = ptx::make_desc(ptx::smem_u32(swe), LBO_B, 128);
         const uint64_t de0 = ptx::make_desc(ptx::smem_u32(i2c), LBO_E, 128);
         // input convolution of board number m (of this CTA) into the accumulator buffer that board will use
+        CV_T(const long long tk0 = clock64(); long long w_e = 0, w_a0 = 0, w_a1 = 0, w_acc = 0, w_b = 0;)
         auto issue_conv0 = [&](uint32_t m) {
+            CV_T(const long long t0 = clock64();)
             ptx::mbar_wait(e_full, m & 1);
+            CV_T(w_e += clock64() - t0;)
             ptx::tc_fence_after();
             const uint32_t acc = tmem_base + (m & 1) * 2 * COUT;
 #pragma unroll
@@ -1692,19 +1695,25 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
                 const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
                 const uint32_t j = 2 * it + chunk, hb = j % 3;
                 if (tap == 0) {      // half slab written by epilogue 0 (which has then also left the accumulator)
+                    CV_T(const long long t0 = clock64();)
                     ptx::mbar_wait(&a_full[hb], (j / 3) & 1);
+                    CV_T(if (chunk == 0) w_a0 += clock64() - t0; else w_a1 += clock64() - t0;)
                     ptx::tc_fence_after();
                 }
                 if (kk == 10 && bn < G) {
                     // the next board's input convolution goes into the other accumulator buffer, free once the main
                     // epilogue of board it - 1 has read it; its epilogue 0 needs the half slab this board's first nine
                     // K steps have just released (and the third one), so it is issued right behind them
+                    CV_T(const long long t0 = clock64();)
                     if (it >= 1) ptx::mbar_wait(&acc_empty[ab ^ 1], ((it - 1) >> 1) & 1);
+                    CV_T(w_acc += clock64() - t0;)
                     ptx::tc_fence_after();
                     issue_conv0(it + 1);
                 }
                 const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + hb * C::HALF_BYTES), LBO_A, 128);
+                CV_T(const long long t2 = clock64();)
                 ptx::mbar_wait(&b_full[wstage], wphase);
+                CV_T(w_b += clock64() - t2;)
                 ptx::tc_fence_after();
                 const uint64_t db0 = ptx::make_desc(ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES), LBO_B, 128);
 #pragma unroll
@@ -1722,6 +1731,9 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ++it;
             b = bn;
         }
+        CV_T(if (blockIdx.x == 0 && lane == 0 && it > 0)
+                 printf("pv0 issuer: %u boards, total %lld | per board: wait e_full %lld, a_full first half %lld, second half %lld, acc_empty (conv0) %lld, b_full (18 waits) %lld\n",
+                        it, clock64() - tk0, w_e / it, w_a0 / it, w_a1 / it, w_acc / it, w_b / it);)
     } else if (warp >= 6) {
         // ================= epilogue 0: input convolution (TMEM) -> bias, ReLU, bf16 -> the 3x3's input slab =================
         const int q = warp & 3, h0 = (warp - 6) >> 2;
@@ -1729,12 +1741,16 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
         const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
         const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h0 * COUT;
         uint32_t it = 0;
+        CV_T(long long e_w0 = 0, e_w1 = 0, e_work = 0;)
         for (int b = first_board(); b < G; b = next_board(b), ++it) {
             const int ab = it & 1;
             const uint32_t j0 = 2 * it, j1 = 2 * it + 1;
+            CV_T(const long long t0 = clock64();)
             ptx::mbar_wait(&de_full[ab], (it >> 1) & 1);
+            CV_T(const long long t1 = clock64(); e_w0 += t1 - t0;)
             ptx::mbar_wait(&a_empty[j0 % 3], ((j0 / 3) & 1) ^ 1);     // the UMMAs that read these two ring slots are done
             ptx::mbar_wait(&a_empty[j1 % 3], ((j1 / 3) & 1) ^ 1);
+            CV_T(const long long t2 = clock64(); e_w1 += t2 - t1;)
             ptx::tc_fence_after();
             uint8_t *dst0 = slab + (j0 % 3) * C::HALF_BYTES + (size_t)(pos + 1) * 16;      // channels 0-63
             uint8_t *dst1 = slab + (j1 % 3) * C::HALF_BYTES + (size_t)(pos + 1) * 16;      // channels 64-127
@@ -1761,7 +1777,10 @@ k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) { ptx::mbar_arrive(&a_full[j0 % 3]); ptx::mbar_arrive(&a_full[j1 % 3]); }
+            CV_T(e_work += clock64() - t2;)
         }
+        CV_T(if (blockIdx.x == 0 && lane == 0 && warp == 6 && it > 0)
+                 printf("pv0 epilogue 0: per board: wait de_full %lld, a_empty %lld, work %lld\n", e_w0 / it, e_w1 / it, e_work / it);)
     } else {
         // ================= main epilogue (warps 2-5, both M halves each): bias, ReLU, bf16 planes =================
         const int q = warp & 3;

@@ -12,7 +12,7 @@ if "--build-only" in sys.argv or not os.path.exists(SO):
     b.build(out=SO, extra_flags=["-DGZ_CONV_TIMING"])
     if "--build-only" in sys.argv:
         sys.exit(0)
-os.environ["GZ_PV_FUSED_CONV0"] = "0"
+os.environ["GZ_PV_FUSED_CONV0"] = "1" if "--fused" in sys.argv else "0"
 import torch
 import engine, workload, bench
 engine.load_library(SO)
