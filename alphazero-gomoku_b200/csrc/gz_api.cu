@@ -240,7 +240,7 @@ static void pack_conv0_bf16(std::vector<uint16_t> &out, const float *w, const fl
                     f2bf((float)((double)w[((size_t)co * 3 + ci) * 9 + tap] * scale));
         }
 }
-// An input convolution [cout][3][3][3] (+ BN) as ONE im2col GEMM operand (k_gn_block0_embed, k_pv_conv0_tower0): K = 27
+// An input convolution [cout][3][3][3] (+ BN) as ONE im2col GEMM operand (k_gn_block0_embed): K = 27
 // padded to 32, in the order the kernels' producers build the one-hot tile in: k = 3 * (3 * plane + ky) + kx (plane =
 // black / white / empty) -> [4 k-groups][cout][8 k] bf16
 static void pack_conv0_im2col_bf16(std::vector<uint16_t> &out, const float *w, const float *bn, int cout) {
@@ -331,13 +331,10 @@ extern "C" int gz_set_pv_weights(gz_handle h, const float *f, int64_t n) {
         }
         size_t off0 = bf.size() * 2;
         pack_conv0_bf16(bf, f, f + 3456 + 128, 128);
-        size_t off_i2c = bf.size() * 2;
-        pack_conv0_im2col_bf16(bf, f, f + 3456 + 128, 128);
         rc = upload_bytes(bf.data(), bf.size() * 2, &e->bw.pv_blob);
         if (rc) return rc;
         for (int i = 0; i < 4; ++i) e->bw.pv_tower_w[i] = e->bw.pv_blob + off[i];
         e->bw.pv_conv0_w = e->bw.pv_blob + off0;
-        e->bw.pv_conv0_i2c_w = e->bw.pv_blob + off_i2c;
     }
     {   // head FCs for gz_nn_fc.cu: policy 450 -> 225 (8 chunks, N 256), value 225 -> 64 (4 chunks, N 64), bias [256]
         const float *q = f + 3456 + 128 + 512 + 2 * (2 * (147456 + 128) + 2 * 512);

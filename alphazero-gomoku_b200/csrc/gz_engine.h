@@ -90,7 +90,6 @@ struct Bf16Weights {
     float gn_host_head[130];      // GraphNet head 1x1: w[64][2] (device layout of hconv_w), b[2]
     float gn_host_embed_bias[64]; // GraphNet embed bias, for k_gn_block0_embed's parameter block
     uint8_t *gn_embed_i2c_w;      // embed weights as ONE K = 32 GEMM operand: [4 k-groups][64 cout][8 k], k = 3 * (3 * plane + ky) + kx
-    uint8_t *pv_conv0_i2c_w;      // the same form of the policy-value input convolution (cout 128, BN folded)
     uint8_t *pv_tower_w[4];
     uint8_t *gn_l3_w[4];
     uint8_t *gn_l3p_w[4];   // the same 3x3 weights in k_gn_block_pairs' order: 3 x [dx=0 | dx=-1] stacked along N, 3 x dx=+1

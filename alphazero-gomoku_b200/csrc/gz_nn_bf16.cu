@@ -1113,8 +1113,8 @@ k_gn_block_pairs(const uint8_t *__restrict__ in_planes, const uint8_t *__restric
 }
 
 // ------------------------------------------------------------------------------------------------
-// im2col one-hot tile of an input convolution (3 planes x 3 x 3 = 27 inputs per position, K padded to 32), shared by
-// k_gn_block0_embed and k_pv_conv0_tower0.  Tile = [4 k-groups][256 rows][8 k] bf16, row = board bit index 16 * row +
+// im2col one-hot tile of an input convolution (3 planes x 3 x 3 = 27 inputs per position, K padded to 32) for
+// k_gn_block0_embed.  Tile = [4 k-groups][256 rows][8 k] bf16, row = board bit index 16 * row +
 // col (= plane position - 16), K index k = 3 * (3 * plane + ky) + kx (pack_conv0_im2col_bf16 packs the weights in the
 // same order).  A warp builds one M half (rows [128 HH, 128 HH + 128)); every lane holds the whole position.
 struct I2cPlanes { uint32_t X[3][11]; };   // X[c][1 + j] = word j of plane c (black, white, empty); X[c][0, 9, 10] = 0
@@ -1536,291 +1536,6 @@ k_gn_block0_embed(const gz_board *__restrict__ boards, const uint8_t *__restrict
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
 }
 
-// ------------------------------------------------------------------------------------------------
-// k_pv_conv0_tower0: the policy-value net's input convolution (3 -> 128, 3x3, BN, ReLU; neural_network.py:136) fused into
-// the first tower convolution, the way k_gn_block0_embed fuses GraphNet's embed: as a launch of its own it wrote 302 MB
-// per wave that the first tower layer read straight back (58 us).  The planes are still written -- they are the skip
-// tensor of the first residual block -- but beside 144 UMMAs per board instead of in an HBM-write-bound kernel of their
-// own, and the read is gone.  Per board: two producer warps build the im2col
-// one-hot tile, ONE K = 32 GEMM (2 N = 128 UMMAs per M half) puts the 128-channel result into the accumulator buffer
-// the board is going to use -- idle between the main epilogue of board it - 2 and the board's own first tap --, eight
-// epilogue-0 warps apply bias + ReLU and write bf16 into the 3x3's input slab in shared memory; the 144 tap UMMAs and
-// the main epilogue are k_conv_umma<128, 128, 9>'s (half slabs, chunk-major K order).  Weights stream through a 5-stage
-// ring (the im2col tile and its weights take the sixth stage's shared memory).
-//   warp 0      weight ring producer          warp 1       tcgen05.mma issuer (both M halves)
-//   warps 2-5   main epilogue (bias, ReLU, bf16 planes to HBM)
-//   warps 6-13  epilogue 0: quadrant = warp & 3, M half = (warp - 6) >> 2        warps 14, 15  im2col producers
-struct PvFusedCfg {
-    static constexpr int CG = 16, SLAB_ROWS = 290, SLAB_BYTES = CG * SLAB_ROWS * 16;
-    static constexpr int HALF_BYTES = SLAB_BYTES / 2;       // three half slabs of 64 channels, K steps chunk-major (ConvCfg::HALVES)
-    static constexpr int KSTEPS = 18, WSTEP_BYTES = 8 * 128 * 16, NSTAGE = 5;
-    static constexpr int I2C_BYTES = 4 * 256 * 16, WE_BYTES = 4 * 128 * 16;
-    static constexpr int THREADS = 512;
-    static constexpr int SMEM = 3 * HALF_BYTES + NSTAGE * WSTEP_BYTES + I2C_BYTES + WE_BYTES + 2 * 128 * 4 + 512;
-};
-
-__global__ void __launch_bounds__(PvFusedCfg::THREADS, 1)
-k_pv_conv0_tower0(const gz_board *__restrict__ boards, const uint8_t *__restrict__ we, const float *__restrict__ bias0,
-                  const uint8_t *__restrict__ w_packed, const float *__restrict__ bias,
-                  uint8_t *__restrict__ conv0_planes, uint8_t *__restrict__ out_planes,
-                  const uint8_t *__restrict__ active, int G, int rev) {
-    using C = PvFusedCfg;
-    constexpr int COUT = 128;
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *slab = smem;                                   // [3][HALF_BYTES]: half slab number j = 2 * board + chunk in slot j % 3
-    uint8_t *wbuf = slab + 3 * C::HALF_BYTES;               // [NSTAGE][WSTEP_BYTES]
-    uint8_t *i2c = wbuf + C::NSTAGE * C::WSTEP_BYTES;       // one tile (the embed kernel has two: this one is over budget)
-    uint8_t *swe = i2c + C::I2C_BYTES;
-    float *sbias = reinterpret_cast<float *>(swe + C::WE_BYTES);
-    float *sbias0 = sbias + COUT;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sbias0 + COUT);
-    uint64_t *a_full = bars, *a_empty = bars + 3, *acc_full = bars + 6, *acc_empty = bars + 8;
-    uint64_t *b_full = bars + 10, *b_empty = bars + 16;
-    uint64_t *e_full = bars + 22, *e_empty = bars + 23, *de_full = bars + 24, *we_full = bars + 26;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 27);
-
-    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
-    auto ph = [&](int b) { return rev ? G - 1 - b : b; };
-    auto next_board = [&](int b) {
-        for (b += gridDim.x; b < G && active && !active[ph(b)]; b += gridDim.x) {}
-        return b;
-    };
-    auto first_board = [&]() {
-        const int b = blockIdx.x;
-        return b < G && active && !active[ph(b)] ? next_board(b) : b;
-    };
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < 3; ++i) {
-            ptx::mbar_init(&a_full[i], 8);      // half slab: written by the 8 epilogue-0 warps
-            ptx::mbar_init(&a_empty[i], 1);
-        }
-        for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&acc_full[i], 1);
-            ptx::mbar_init(&acc_empty[i], 4);
-            ptx::mbar_init(&de_full[i], 1);
-        }
-        for (int i = 0; i < C::NSTAGE; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
-        ptx::mbar_init(e_full, 2);              // im2col tile: two producer warps
-        ptx::mbar_init(e_empty, 1);
-        ptx::mbar_init(we_full, 1);
-        ptx::fence_mbar_init();
-    }
-    for (int i = threadIdx.x; i < COUT; i += C::THREADS) { sbias[i] = bias[i]; sbias0[i] = bias0[i]; }
-    // the slab rows outside the board (and everything epilogue 0 never writes) stay zero for the whole kernel
-    for (int i = threadIdx.x; i < 3 * C::HALF_BYTES / 16; i += C::THREADS)
-        reinterpret_cast<uint4 *>(slab)[i] = make_uint4(0u, 0u, 0u, 0u);
-    ptx::fence_proxy_async();
-    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
-    ptx::tc_fence_before();
-    __syncthreads();
-    ptx::tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-
-    if (warp == 0) {
-        // ================= weight ring: 18 K steps of 16 KB per board, from L2 =================
-        if (lane == 0) {
-            ptx::mbar_expect_tx(we_full, C::WE_BYTES);
-            ptx::bulk_g2s(swe, we, C::WE_BYTES, we_full);
-            uint32_t wstage = 0, wphase = 0;
-            for (int b = first_board(); b < G; b = next_board(b)) {
-                for (int kk = 0; kk < C::KSTEPS; ++kk) {
-                    const int ks = (kk % 9) * 2 + kk / 9;       // chunk-major order; the pack is tap-major
-                    ptx::mbar_wait(&b_empty[wstage], wphase ^ 1);
-                    ptx::mbar_expect_tx(&b_full[wstage], C::WSTEP_BYTES);
-                    ptx::bulk_g2s(wbuf + wstage * C::WSTEP_BYTES, w_packed + (size_t)ks * C::WSTEP_BYTES, C::WSTEP_BYTES,
-                                  &b_full[wstage]);
-                    if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
-                }
-            }
-        }
-    } else if (warp >= 14) {
-        // ================= im2col producers: M half 0 / 1; the next board's words are fetched one board ahead =================
-        const int hh = warp - 14;
-        auto load_words = [&](int b, uint4 *q) {
-            if (b < G) {
-                const uint4 *src = reinterpret_cast<const uint4 *>(boards[ph(b)].stones);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) q[i] = src[i];
-            }
-        };
-        uint4 q[4];
-        int b = first_board();
-        load_words(b, q);
-        for (uint32_t it = 0; b < G; ++it) {
-            I2cPlanes P;
-            im2col_planes(q, P);
-            b = next_board(b);
-            load_words(b, q);
-            if (lane == 0) ptx::mbar_wait(e_empty, (it & 1) ^ 1);
-            __syncwarp();
-            if (hh == 0) im2col_write_half<0>(P, i2c, lane); else im2col_write_half<1>(P, i2c, lane);
-            ptx::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(e_full);
-        }
-    } else if (warp == 1) {
-        // ================= tcgen05.mma issuer =================
-        constexpr uint32_t idesc = ptx::make_idesc_bf16(128, COUT);
-        constexpr uint32_t LBO_A = C::SLAB_ROWS * 16, LBO_B = COUT * 16, LBO_E = 256 * 16;
-        ptx::mbar_wait(we_full, 0);
-        const uint64_t dwe0 = ptx::make_desc(ptx::smem_u32(swe), LBO_B, 128);
-        const uint64_t de0 = ptx::make_desc(ptx::smem_u32(i2c), LBO_E, 128);
-        // input convolution of board number m (of this CTA) into the accumulator buffer that board will use
-        CV_T(const long long tk0 = clock64(); long long w_e = 0, w_a0 = 0, w_a1 = 0, w_acc = 0, w_b = 0;)
-        auto issue_conv0 = [&](uint32_t m) {
-            CV_T(const long long t0 = clock64();)
-            ptx::mbar_wait(e_full, m & 1);
-            CV_T(w_e += clock64() - t0;)
-            ptx::tc_fence_after();
-            const uint32_t acc = tmem_base + (m & 1) * 2 * COUT;
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-#pragma unroll
-                for (int ks = 0; ks < 2; ++ks)
-                    ptx::umma_bf16_elect(acc + h * COUT, de0 + (uint64_t)(2 * ks * 256 + 128 * h),
-                                         dwe0 + (uint64_t)((2 * ks * (int)LBO_B) >> 4), idesc, ks != 0);
-            ptx::umma_commit_elect(e_empty);
-            ptx::umma_commit_elect(&de_full[m & 1]);
-        };
-        uint32_t it = 0, wstage = 0, wphase = 0;
-        int b = first_board();
-        if (b < G) issue_conv0(0);
-        while (b < G) {
-            const int bn = next_board(b);
-            const int ab = it & 1;
-            const uint32_t acc = tmem_base + ab * 2 * COUT;
-#pragma unroll
-            for (int kk = 0; kk < C::KSTEPS; ++kk) {
-                const int chunk = kk / 9, tap = kk - 9 * chunk;
-                const int rowoff = 17 + 16 * (tap / 3 - 1) + (tap % 3 - 1);
-                const uint32_t j = 2 * it + chunk, hb = j % 3;
-                if (tap == 0) {      // half slab written by epilogue 0 (which has then also left the accumulator)
-                    CV_T(const long long t0 = clock64();)
-                    ptx::mbar_wait(&a_full[hb], (j / 3) & 1);
-                    CV_T(if (chunk == 0) w_a0 += clock64() - t0; else w_a1 += clock64() - t0;)
-                    ptx::tc_fence_after();
-                }
-                if (kk == 10 && bn < G) {
-                    // the next board's input convolution goes into the other accumulator buffer, free once the main
-                    // epilogue of board it - 1 has read it; its epilogue 0 needs the half slab this board's first nine
-                    // K steps have just released (and the third one), so it is issued right behind them
-                    CV_T(const long long t0 = clock64();)
-                    if (it >= 1) ptx::mbar_wait(&acc_empty[ab ^ 1], ((it - 1) >> 1) & 1);
-                    CV_T(w_acc += clock64() - t0;)
-                    ptx::tc_fence_after();
-                    issue_conv0(it + 1);
-                }
-                const uint64_t da0 = ptx::make_desc(ptx::smem_u32(slab + hb * C::HALF_BYTES), LBO_A, 128);
-                CV_T(const long long t2 = clock64();)
-                ptx::mbar_wait(&b_full[wstage], wphase);
-                CV_T(w_b += clock64() - t2;)
-                ptx::tc_fence_after();
-                const uint64_t db0 = ptx::make_desc(ptx::smem_u32(wbuf + wstage * C::WSTEP_BYTES), LBO_B, 128);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        ptx::umma_bf16_elect(acc + h * COUT, da0 + (uint64_t)(2 * k * C::SLAB_ROWS + rowoff + 128 * h),
-                                             db0 + (uint64_t)((2 * k * (int)LBO_B) >> 4), idesc, (kk | k) != 0);
-                }
-                ptx::umma_commit_elect(&b_empty[wstage]);
-                if (++wstage == C::NSTAGE) { wstage = 0; wphase ^= 1; }
-                if (tap == 8) ptx::umma_commit_elect(&a_empty[hb]);
-            }
-            ptx::umma_commit_elect(&acc_full[ab]);
-            ++it;
-            b = bn;
-        }
-        CV_T(if (blockIdx.x == 0 && lane == 0 && it > 0)
-                 printf("pv0 issuer: %u boards, total %lld | per board: wait e_full %lld, a_full first half %lld, second half %lld, acc_empty (conv0) %lld, b_full (18 waits) %lld\n",
-                        it, clock64() - tk0, w_e / it, w_a0 / it, w_a1 / it, w_acc / it, w_b / it);)
-    } else if (warp >= 6) {
-        // ================= epilogue 0: input convolution (TMEM) -> bias, ReLU, bf16 -> the 3x3's input slab =================
-        const int q = warp & 3, h0 = (warp - 6) >> 2;
-        const int pos = 16 + 128 * h0 + 32 * q + lane;
-        const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
-        const uint32_t tlane = tmem_base + ((uint32_t)(32 * q) << 16) + h0 * COUT;
-        uint32_t it = 0;
-        CV_T(long long e_w0 = 0, e_w1 = 0, e_work = 0;)
-        for (int b = first_board(); b < G; b = next_board(b), ++it) {
-            const int ab = it & 1;
-            const uint32_t j0 = 2 * it, j1 = 2 * it + 1;
-            CV_T(const long long t0 = clock64();)
-            ptx::mbar_wait(&de_full[ab], (it >> 1) & 1);
-            CV_T(const long long t1 = clock64(); e_w0 += t1 - t0;)
-            ptx::mbar_wait(&a_empty[j0 % 3], ((j0 / 3) & 1) ^ 1);     // the UMMAs that read these two ring slots are done
-            ptx::mbar_wait(&a_empty[j1 % 3], ((j1 / 3) & 1) ^ 1);
-            CV_T(const long long t2 = clock64(); e_w1 += t2 - t1;)
-            ptx::tc_fence_after();
-            uint8_t *dst0 = slab + (j0 % 3) * C::HALF_BYTES + (size_t)(pos + 1) * 16;      // channels 0-63
-            uint8_t *dst1 = slab + (j1 % 3) * C::HALF_BYTES + (size_t)(pos + 1) * 16;      // channels 64-127
-            // the planes also go to HBM: they are the skip tensor of the first residual block (neural_network.py:139-141)
-            uint8_t *gdst = conv0_planes + kGuardBytes + (size_t)ph(b) * (COUT / 8) * kPlaneBytes + (size_t)pos * 16;
-#pragma unroll
-            for (int c64 = 0; c64 < COUT; c64 += 64) {
-                float v[64];
-                ptx::tmem_ld64(tlane + ab * 2 * COUT + c64, v);
-#pragma unroll
-                for (int c0 = 0; c0 < 64; c0 += 8) {
-                    uint32_t pk[4];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        pk[i] = valid ? ptx::pack_bf16(fmaxf(v[c0 + 2 * i] + sbias0[c64 + c0 + 2 * i], 0.f),
-                                                       fmaxf(v[c0 + 2 * i + 1] + sbias0[c64 + c0 + 2 * i + 1], 0.f)) : 0u;
-                    *reinterpret_cast<uint4 *>((c64 ? dst1 : dst0) + (size_t)(c0 / 8) * C::SLAB_ROWS * 16) =
-                        make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4 *>(gdst + (size_t)((c64 + c0) / 8) * kPlaneBytes) =
-                        make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                }
-            }
-            ptx::fence_proxy_async();
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) { ptx::mbar_arrive(&a_full[j0 % 3]); ptx::mbar_arrive(&a_full[j1 % 3]); }
-            CV_T(e_work += clock64() - t2;)
-        }
-        CV_T(if (blockIdx.x == 0 && lane == 0 && warp == 6 && it > 0)
-                 printf("pv0 epilogue 0: per board: wait de_full %lld, a_empty %lld, work %lld\n", e_w0 / it, e_w1 / it, e_work / it);)
-    } else {
-        // ================= main epilogue (warps 2-5, both M halves each): bias, ReLU, bf16 planes =================
-        const int q = warp & 3;
-        uint32_t it = 0;
-        for (int b = first_board(); b < G; b = next_board(b), ++it) {
-            const int ab = it & 1;
-            ptx::mbar_wait(&acc_full[ab], (it >> 1) & 1);
-            ptx::tc_fence_after();
-            const size_t obase = kGuardBytes + (size_t)ph(b) * (COUT / 8) * kPlaneBytes;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int pos = 16 + 128 * h + 32 * q + lane;
-                const bool valid = (pos & 15) != 15 && (pos >> 4) <= 15;
-                const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + ab * 2 * COUT + h * COUT;
-#pragma unroll 1
-                for (int c0 = 0; c0 < COUT; c0 += 16) {
-                    float v[16];
-                    ptx::tmem_ld16(taddr + c0, v);
-                    const size_t o0 = obase + (size_t)(c0 / 8) * kPlaneBytes + (size_t)pos * 16;
-                    uint32_t pk[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        float x0 = fmaxf(v[2 * i] + sbias[c0 + 2 * i], 0.f);
-                        float x1 = fmaxf(v[2 * i + 1] + sbias[c0 + 2 * i + 1], 0.f);
-                        pk[i] = valid ? ptx::pack_bf16(x0, x1) : 0u;
-                    }
-                    *reinterpret_cast<uint4 *>(out_planes + o0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4 *>(out_planes + o0 + kPlaneBytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                }
-            }
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&acc_empty[ab]);
-        }
-    }
-    ptx::tc_fence_before();
-    __syncthreads();
-    if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
-}
-
 static void launch_gn_block(Engine &e, const uint8_t *in, int block, uint8_t *out, uint8_t *head_out, int G,
                             cudaStream_t s, int direction) {
     static bool configured = false;
@@ -1876,50 +1591,27 @@ static void launch_conv(Engine &e, const uint8_t *in, const uint8_t *w, const fl
                heads, alternate ? rev : 0);
 }
 
-static bool pv_fused_conv0() {   // A/B switch: GZ_PV_FUSED_CONV0=0 keeps the input convolution as a launch of its own
-    static const bool on = !(getenv("GZ_PV_FUSED_CONV0") && atoi(getenv("GZ_PV_FUSED_CONV0")) == 0);
-    return on;
-}
-// input convolution + first tower convolution in one launch: boards -> p0 (skip tensor) and p1
-static void launch_pv_conv0_tower0(Engine &e, const gz_board *boards, const uint8_t *active, int G, cudaStream_t s) {
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(k_pv_conv0_tower0, cudaFuncAttributeMaxDynamicSharedMemorySize, PvFusedCfg::SMEM);
-        configured = true;
-    }
-    const int grid = G < e.sm_count ? G : e.sm_count;
-    k_pv_conv0_tower0<<<grid, PvFusedCfg::THREADS, PvFusedCfg::SMEM, s>>>(boards, e.bw.pv_conv0_i2c_w, e.pv.conv0.b,
-                                                                          e.bw.pv_tower_w[0], e.pv.tower[0].b, e.planes[0],
-                                                                          e.planes[1], active, G, 0);
-}
-
 void nn_pv_forward_bf16(Engine &e, const gz_board *boards, const uint8_t *active, int G,
                         float *logits, float *probs, float *value, float *prior_out,
                         const int32_t *prior_slot, cudaStream_t s) {
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1], *p2 = e.planes[2];
+    prof_begin(e, GZ_STAGE_PV_CONV0, 1, s);
+    launch_conv<16, 128, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.pv_conv0_w,
+                                               e.pv.conv0.b, nullptr, p0, active, G, s);
+    prof_end(e, s);
+    // board direction alternates layer by layer (the input convolution walks forward): see k_conv_umma's `rev`.
+    // The input convolution stays a launch of its own: fused into the first tower layer the way k_gn_block0_embed
+    // fuses GraphNet's embed it measured no gain -- the tower's N = 128 UMMAs already take all of the shared-memory
+    // bandwidth (8 KB of operands per 64 cycles), and the fused epilogue's slab writes crawled behind them (8.1 k cycles
+    // per board): DESIGN.md section 5, profiles/r02_pv_fused_conv0.md.
+    prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
+    launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s, HeadConv(), 1);
+    launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s, HeadConv(), 0);
+    launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s, HeadConv(), 1);
     HeadConv hc = {e.pv.pconv_w, e.pv.pconv_b, e.pv.vconv_w, e.pv.vconv_b, e.pv_pc, e.pv_vc};
-    // board direction alternates layer by layer: see k_conv_umma's `rev`
-    if (pv_fused_conv0()) {
-        // boards -> p0 (input convolution, the first block's skip tensor) and p1 (first tower convolution) in one launch
-        prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
-        launch_pv_conv0_tower0(e, boards, active, G, s);
-        launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s, HeadConv(), 1);
-        launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s, HeadConv(), 0);
-        launch_conv<128, 128, 9, false, true, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s, hc, 1);
-        prof_end(e, s);
-    } else {
-        prof_begin(e, GZ_STAGE_PV_CONV0, 1, s);
-        launch_conv<16, 128, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.pv_conv0_w,
-                                                   e.pv.conv0.b, nullptr, p0, active, G, s);
-        prof_end(e, s);
-        prof_begin(e, GZ_STAGE_PV_TOWER, 4, s);
-        launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, active, G, s, HeadConv(), 1);
-        launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, active, G, s, HeadConv(), 0);
-        launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, active, G, s, HeadConv(), 1);
-        launch_conv<128, 128, 9, false, true, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s, hc, 0);
-        prof_end(e, s);
-    }
+    launch_conv<128, 128, 9, false, true, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, active, G, s, hc, 0);
+    prof_end(e, s);
     nn_heads_bf16(e, true, boards, active, G, nullptr, logits, probs, value, prior_out, prior_slot, s);
 }
 
@@ -1964,15 +1656,10 @@ void nn_debug_planes_to_nchw(Engine &e, int which, int C, int G, float *out, cud
 void nn_debug_pv_layer_bf16(Engine &e, const gz_board *boards, int G, int nlayers, float *out, cudaStream_t s) {
     const Bf16Weights &w = e.bw;
     uint8_t *p0 = e.planes[0], *p1 = e.planes[1], *p2 = e.planes[2];
+    launch_conv<16, 128, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.pv_conv0_w,
+                                               e.pv.conv0.b, nullptr, p0, nullptr, G, s);
     int last = 0;
-    if (pv_fused_conv0() && nlayers >= 1) {      // the fused kernel writes both the input convolution (p0) and layer 1 (p1)
-        launch_pv_conv0_tower0(e, boards, nullptr, G, s);
-        last = 1;
-    } else {
-        launch_conv<16, 128, 9, true, false, true>(e, reinterpret_cast<const uint8_t *>(boards), w.pv_conv0_w,
-                                                   e.pv.conv0.b, nullptr, p0, nullptr, G, s);
-        if (nlayers >= 1) { launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, nullptr, G, s); last = 1; }
-    }
+    if (nlayers >= 1) { launch_conv<128, 128, 9, false, false>(e, p0, w.pv_tower_w[0], e.pv.tower[0].b, nullptr, p1, nullptr, G, s); last = 1; }
     if (nlayers >= 2) { launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[1], e.pv.tower[1].b, p0, p2, nullptr, G, s); last = 2; }
     if (nlayers >= 3) { launch_conv<128, 128, 9, false, false>(e, p2, w.pv_tower_w[2], e.pv.tower[2].b, nullptr, p1, nullptr, G, s); last = 1; }
     if (nlayers >= 4) { launch_conv<128, 128, 9, false, true>(e, p1, w.pv_tower_w[3], e.pv.tower[3].b, p2, p0, nullptr, G, s); last = 0; }

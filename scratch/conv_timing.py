@@ -1,6 +1,5 @@
 """Where k_conv_umma<128,128,9>'s issuer and epilogue warps wait: an instrumented copy of the library (-DGZ_CONV_TIMING),
-one policy-value forward on 4096 boards with the input convolution as its own launch so that all four tower layers
-run through k_conv_umma.  Diagnostic, not a benchmark.  Build here: python scratch/conv_timing.py --build-only"""
+one policy-value forward on 4096 boards.  Diagnostic, not a benchmark.  Build here: python scratch/conv_timing.py --build-only"""
 import importlib.util, os, sys
 ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 PKG = os.path.join(ROOT, "alphazero-gomoku_b200")
@@ -12,7 +11,6 @@ if "--build-only" in sys.argv or not os.path.exists(SO):
     b.build(out=SO, extra_flags=["-DGZ_CONV_TIMING"])
     if "--build-only" in sys.argv:
         sys.exit(0)
-os.environ["GZ_PV_FUSED_CONV0"] = "1" if "--fused" in sys.argv else "0"
 import torch
 import engine, workload, bench
 engine.load_library(SO)
