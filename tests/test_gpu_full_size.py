@@ -79,3 +79,35 @@ def test_config3_hard_4096_games_sharding_invariance(weights):
         assert np.array_equal(cv_h, cv[lo:hi]) and np.array_equal(cval_h, cval[lo:hi])
         assert np.array_equal(best_h, best[lo:hi])
     eng.close()
+
+
+def test_large_batch_16384_games_matches_small_slices(weights):
+    """Capacity beyond the benchmark sizes (BASELINE config 4 runs 8192 games per GPU; DESIGN.md 4 sizes 65 536): 16 384
+    concurrent games put 110-111 boards on every CTA of the persistent tensor kernels (barrier phases wrap dozens of
+    times, every ring slot is reused).  Slices of 128 games taken from the start, the middle and the end must reproduce
+    the big call bit for bit when they are searched alone with the same global game ids -- bf16 networks, Philox
+    randomness, planner-guided playouts -- and the policy-value outputs of those boards must be identical too."""
+    import engine
+    import workload
+    G, S = 16384, 6
+    eng = engine.Engine(max_games=G, max_simulations=8, precision=1)
+    eng.set_pv_weights(weights["pv"])
+    eng.set_planner_weights(weights["graphnet"], weights["dqn"])
+    cells, tm, mc = workload.make_positions(G, seed=11)
+
+    def run(lo, hi):
+        p = engine.make_params(S, 1.8, beta=0.2, planner_steps=3, difficulty="hard", deterministic=False,
+                               seed=0x16384, game_base=lo)
+        return eng.search_host(cells[lo:hi], tm[lo:hi], mc[lo:hi], tm[lo:hi], p)
+
+    cv, cval, best = run(0, G)
+    assert eng.counters()["simulations"] == G * S
+    boards = eng.boards_from_cells(cells, tm, mc)
+    lg, pr, v = (t.cpu().numpy() for t in eng.pv_forward(boards))
+    for lo in (0, 8064, G - 128):
+        cv_s, cval_s, best_s = run(lo, lo + 128)
+        assert np.array_equal(cv_s, cv[lo:lo + 128]) and np.array_equal(cval_s, cval[lo:lo + 128]), lo
+        assert np.array_equal(best_s, best[lo:lo + 128]), lo
+        lg_s, pr_s, v_s = (t.cpu().numpy() for t in eng.pv_forward(boards[lo:lo + 128].clone()))
+        assert np.array_equal(lg_s, lg[lo:lo + 128]) and np.array_equal(v_s, v[lo:lo + 128]), lo
+    eng.close()
